@@ -1,0 +1,296 @@
+#!/usr/bin/env python
+"""Benchmark of the CGNN hot path on B200 (contract: see DESIGN.md "Measurement").
+
+One "step" = one batch of the synthetic pairwise sweep of BASELINE.json configs[3]
+(cause-effect pairs, n=1500 rows, nb_runs=32, h=30, 1000 train + 500 eval steps per instance,
+both directions): `--pairs` pairs per GPU per step = pairs*32*2 generator instances, scored by
+ONE launch of the persistent instance kernel.
+
+  value  : generator train-steps/s, whole job, inputs already resident in HBM
+  e2e    : the same through the public Python API with HOST buffers (H2D + D2H inside)
+  roofline: algorithmic exp/s of the instance kernel vs this chip's measured MUFU peak
+  cpu_baseline: the fp32 torch-CPU restatement of the reference graph on the host cores
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference]
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import tempfile
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+N_ROWS, H, NB_RUNS, TRAIN, TEST = 1500, 30, 32, 1000, 500
+METRIC = "MMD train-steps/sec (n=1500)"
+UNIT = "train-steps/s"
+
+
+def algorithmic_work(n_inst, n=N_ROWS, train=TRAIN, test=TEST):
+    """kernel evaluations P = N^2 (pred-true) + N(N-1)/2 (pred-pred) per step, 7 exps
+    each; plus the once-per-instance true-true block N(N+1)/2.  Returns (exps, fp32 flops) per launch."""
+    P = n * n + n * (n - 1) // 2
+    d = 2
+    f_train = n * n * (5 * d + 28) + (n * (n - 1) // 2) * (7 * d + 28)
+    f_eval = (3 * d + 14) * P
+    exps = n_inst * (7 * P * (train + test) + 7 * (n * (n + 1) // 2))
+    flops = n_inst * (train * f_train + test * f_eval)
+    return exps, flops
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons DURING the timed region (B200_PROFILING.md recipe)."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
+         "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index):
+        self.idx = gpu_index
+        self.f = tempfile.NamedTemporaryFile("w+", suffix=".csv", delete=False)
+        self.p = None
+
+    def start(self):
+        try:
+            self.p = subprocess.Popen(["nvidia-smi", "-i", str(self.idx), "--query-gpu=" + self.Q,
+                                       "--format=csv,noheader,nounits", "-lms", "200"],
+                                      stdout=self.f, stderr=subprocess.DEVNULL)
+        except OSError:
+            self.p = None
+
+    def stop(self):
+        if self.p is None:
+            return dict(sm_mhz=None, sm_max_mhz=None, reasons=["nvidia-smi unavailable"])
+        self.p.terminate()
+        try:
+            self.p.wait(timeout=5)
+        except subprocess.TimeoutExpired:
+            self.p.kill()
+        self.f.flush()
+        self.f.seek(0)
+        sm, mx, reasons, pw = [], [], set(), []
+        for line in self.f.read().splitlines():
+            c = [x.strip() for x in line.split(",")]
+            if len(c) < 9:
+                continue
+            try:
+                sm.append(float(c[1])); mx.append(float(c[2])); pw.append(float(c[3]))
+            except ValueError:
+                continue
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), c[5:9]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        os.unlink(self.f.name)
+        if not sm:
+            return dict(sm_mhz=None, sm_max_mhz=None, reasons=["no samples"])
+        return dict(sm_mhz=float(np.median(sm)), sm_max_mhz=float(max(mx)), reasons=sorted(reasons),
+                    power_w_max=float(max(pw)), samples=len(sm))
+
+
+def cpu_baseline_sample(train_steps, eval_steps, n_instances=None):
+    """Timed CPU port on a bounded sample; returns train-steps/s for the 1000:500 train:eval mix."""
+    from cgnn_b200 import synth
+    from oracle import cpu_baseline
+    xy, _ = synth.make_pair(0, N_ROWS)
+    r = cpu_baseline.time_pairwise_sample(xy, H, n_instances, train_steps, eval_steps)
+    per_instance_s = TRAIN * r["per_train_step_s"] + TEST * r["per_eval_step_s"]   # one core, one instance
+    value = r["cores"] * TRAIN / per_instance_s
+    sample = ("%d instances x (%d train + %d eval) steps, N=%d h=%d, fp32 torch-CPU restatement of the TF graph, "
+              "joblib n_jobs=%d x 1 thread; scaled to the 1000:500 train:eval mix"
+              % (r["n_instances"], train_steps, eval_steps, N_ROWS, H, r["cores"]))
+    return value, r, sample
+
+
+def run_reference(args, rank, world):
+    """--impl reference: the reference's CPU implementation of the path.  TensorFlow is unavailable on
+    this image, so this is the oracle port (kind="port"); rank 0 only."""
+    if rank != 0:
+        return
+    vals = []
+    for s in range(args.warmup + args.steps):
+        t0 = time.perf_counter()
+        v, r, sample = cpu_baseline_sample(2, 1)
+        if s >= args.warmup:
+            vals.append((v, time.perf_counter() - t0))
+    value = float(np.mean([v for v, _ in vals]))
+    ms = float(np.mean([t for _, t in vals]) * 1e3)
+    print(json.dumps({
+        "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": workload_config(args, world),
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": os.cpu_count(), "kind": "port", "sample": sample},
+        "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }))
+
+
+def workload_config(args, world):
+    return {"workload": "synthetic pairwise sweep slice (BASELINE configs[3]): %d pairs/GPU/step x nb_runs=%d x 2 "
+                        "directions, n=%d rows, h=%d, %d train + %d eval steps per instance"
+                        % (args.pairs, NB_RUNS, N_ROWS, H, TRAIN, TEST),
+            "pairs_per_gpu_per_step": args.pairs, "instances_per_step": args.pairs * NB_RUNS * 2 * world,
+            "parallelism": "instances sharded over %d GPU(s), one process per GPU, no data-path collective; "
+                           "final all_gather of scores" % world,
+            "l2_policy": "working set lives in shared memory for the whole launch (HBM/L2 touched once per instance); "
+                         "every step uses fresh pairs, so nothing is served from a previous step's cache",
+            "exp_policy": args.exp_policy}
+
+
+def main():
+    global TRAIN, TEST
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=3)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--pairs", type=int, default=9, help="pairs per GPU per step (9 -> 576 instances ~ 2 per CTA slot)")
+    ap.add_argument("--exp-policy", type=int, default=None)
+    ap.add_argument("--train", type=int, default=TRAIN)
+    ap.add_argument("--test", type=int, default=TEST)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    TRAIN, TEST = args.train, args.test
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+
+    if args.impl == "reference":
+        if args.exp_policy is None:
+            args.exp_policy = -1
+        run_reference(args, rank, world)
+        return
+
+    import torch
+    import torch.distributed as dist
+    from cgnn_b200 import Engine, SETTINGS, synth
+    if args.exp_policy is None:
+        args.exp_policy = SETTINGS.exp_policy
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device - this engine has no CPU fallback")
+    torch.cuda.set_device(local)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    eng = Engine(local)
+    stream = torch.cuda.current_stream()
+    eng.set_stream(stream.cuda_stream)
+
+    total_steps = args.warmup + args.steps
+    kw = dict(n_runs=NB_RUNS, h_layer_dim=H, train_epochs=TRAIN, test_epochs=TEST, exp_policy=args.exp_policy, seed=0)
+    n_inst = args.pairs * NB_RUNS * 2
+
+    # synthetic pairs: every (step, rank) gets its own slice of the sweep
+    def pair_slice(step, leg):
+        first = ((leg * total_steps + step) * world + rank) * args.pairs
+        return first, synth.make_pairs(first, args.pairs, N_ROWS)[0]
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def max_over_ranks(x):
+        if world == 1:
+            return x
+        t = torch.tensor([x], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    # ---- leg 1: inputs resident in HBM ------------------------------------------------------
+    dev_xy, firsts = [], []
+    for s in range(total_steps):
+        first, xy = pair_slice(s, 0)
+        firsts.append(first)
+        dev_xy.append(torch.from_numpy(xy).cuda())
+    dev_scores = torch.empty((args.pairs, NB_RUNS, 2), dtype=torch.float32, device="cuda")
+    gathered = [torch.empty_like(dev_scores) for _ in range(world)] if world > 1 else None
+
+    def device_step(s):
+        eng.run_pairwise(dev_xy[s], uid_base=firsts[s] * NB_RUNS * 2, scores_out=dev_scores, **kw)
+        if world > 1:
+            dist.all_gather(gathered, dev_scores)      # the path's only exchange: final gather of scores
+
+    for s in range(args.warmup):
+        device_step(s)
+    barrier()
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    kernel_ms = []
+    e0.record(stream)
+    for s in range(args.warmup, total_steps):
+        device_step(s)
+        kernel_ms.append(eng.last_kernel_ms)
+    e1.record(stream)
+    barrier()
+    clocks = sampler.stop() if rank == 0 else None
+    dev_ms = max_over_ranks(e0.elapsed_time(e1))
+    launches = args.steps * eng.last_launch_count
+    value = world * n_inst * TRAIN * args.steps / (dev_ms * 1e-3)
+
+    # ---- leg 2: end to end through the public API with host buffers ---------------------------
+    host_xy = [pair_slice(s, 1) for s in range(1 + args.steps)]
+    pinned = [(f, torch.from_numpy(x).pin_memory()) for f, x in host_xy]
+
+    def host_step(s):
+        f, x = pinned[s]
+        r = eng.run_pairwise(x.numpy(), uid_base=f * NB_RUNS * 2, **kw)      # H2D of x, D2H of scores inside
+        sc = r["scores"]
+        if world > 1:
+            t = torch.from_numpy(sc).cuda()
+            dist.all_gather(gathered, t)
+        return sc
+
+    host_step(0)
+    barrier()
+    t0 = time.perf_counter()
+    for s in range(1, 1 + args.steps):
+        sc = host_step(s)
+    barrier()
+    e2e_s = max_over_ranks(time.perf_counter() - t0)
+    e2e_value = world * n_inst * TRAIN * args.steps / e2e_s
+    h2d = int(host_xy[0][1].nbytes + args.pairs * 4 + n_inst * 16)
+    d2h = int(n_inst * 4)
+
+    # ---- roofline of the instance kernel ---------------------------------------------------
+    exps, flops = algorithmic_work(n_inst, N_ROWS, TRAIN, TEST)
+    k_ms = float(np.mean(kernel_ms))
+    mufu_peak = eng.probe_peak("mufu")
+    ffma_peak = eng.probe_peak("ffma")
+    ach_exp = exps / (k_ms * 1e-3)
+    ach_flop = flops / (k_ms * 1e-3)
+    roof = {"bound": "mufu", "achieved": ach_exp / 1e12, "peak": mufu_peak / 1e12, "unit": "Texp/s",
+            "frac": ach_exp / mufu_peak, "traffic": None,
+            "peak_source": "measured live: cgnn_b200_probe_peak (ex2.approx.ftz chains); MEASURED_PEAKS.json has "
+                           "no MUFU/FP32 entry; nominal 148 SM x 16 lanes x 1.965 GHz = 4.65 Texp/s",
+            "fp32": {"achieved_tflops": ach_flop / 1e12, "peak_tflops": ffma_peak / 1e12, "frac": ach_flop / ffma_peak},
+            "kernel_ms_avg": k_ms, "algorithmic_exps_per_launch": exps, "algorithmic_flops_per_launch": flops,
+            "note": "algorithmic count = 7 exp per kernel evaluation (SURVEY 8d); exp_policy=1 issues 5 MUFU "
+                    "per evaluation (gamma 0.5 and 1 by squaring), so frac can exceed the MUFU pipe utilisation"}
+
+    out = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+           "warmup": args.warmup, "ms_per_step": dev_ms / args.steps, "higher_is_better": True, "scaling": "weak",
+           "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": workload_config(args, world),
+           "pair_scores_per_s": world * args.pairs * args.steps / (dev_ms * 1e-3),
+           "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                   "pair_scores_per_s": world * args.pairs * args.steps / e2e_s},
+           "gpu_launches": launches, "clocks": clocks, "roofline": roof}
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        v, r, sample = cpu_baseline_sample(4, 2)
+        out["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": r["cores"], "kind": "port", "sample": sample}
+    if rank == 0:
+        out["score_sanity"] = {"mean": float(np.mean(sc)), "finite": bool(np.all(np.isfinite(sc)))}
+        print(json.dumps(out))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

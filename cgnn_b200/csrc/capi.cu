@@ -1,0 +1,389 @@
+// C-ABI of the cgnn_b200 engine: context, buffer staging, launches.  See include/cgnn_b200.h.
+#include <cuda_runtime.h>
+#include <algorithm>
+#include <cmath>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <numeric>
+#include <string>
+#include <vector>
+
+#include "../../include/cgnn_b200.h"
+#include "pairwise.cuh"
+
+using namespace cgnn;
+
+// ---------------------------------------------------------------------------------------------
+// Pipe-peak micro-benchmarks: 8 independent dependency chains per thread, results kept live.
+__global__ void __launch_bounds__(512) probe_mufu_kernel(float* sink, int iters) {
+    float x[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) x[k] = 0.1f * float(k + 1) + 1e-3f * float(threadIdx.x & 31);
+    for (int it = 0; it < iters; ++it) {
+#pragma unroll
+        for (int k = 0; k < 8; ++k) x[k] = ex2f(-x[k]);     // fixed point ~0.64: stays finite, never constant-folded
+    }
+    float s = 0.f;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) s += x[k];
+    if (s == 123.456f) sink[0] = s;
+}
+__global__ void __launch_bounds__(512) probe_ffma_kernel(float* sink, int iters) {
+    float x[8];
+    const float a = 0.999f + 1e-6f * float(threadIdx.x & 31), b = 1e-3f;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) x[k] = 0.1f * float(k + 1);
+    for (int it = 0; it < iters; ++it) {
+#pragma unroll
+        for (int k = 0; k < 8; ++k) x[k] = fmaf(x[k], a, b);
+    }
+    float s = 0.f;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) s += x[k];
+    if (s == 123.456f) sink[0] = s;
+}
+
+// ---------------------------------------------------------------------------------------------
+struct DevBuf {
+    void* p = nullptr;
+    size_t cap = 0;
+};
+
+struct cgnn_ctx {
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    bool own_stream = true;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    cudaDeviceProp prop{};
+    std::string err;
+    float last_ms = 0.f;
+    int last_launches = 0;
+    int pw_ctas_per_sm = 0;
+    // staging buffers (grow-only)
+    DevBuf xy, nrows, inst, scores, noise, init, trace, pout, counter, dbg[5];
+};
+
+static int fail(cgnn_ctx* c, int code, const char* fmt, ...) {
+    char buf[512];
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(buf, sizeof buf, fmt, ap);
+    va_end(ap);
+    if (c) c->err = buf;
+    return code;
+}
+
+#define CU(call)                                                                                         \
+    do {                                                                                                 \
+        cudaError_t e_ = (call);                                                                         \
+        if (e_ != cudaSuccess)                                                                           \
+            return fail(ctx, e_ == cudaErrorMemoryAllocation ? CGNN_ERR_NOMEM : CGNN_ERR_CUDA, "%s: %s", \
+                        #call, cudaGetErrorString(e_));                                                  \
+    } while (0)
+
+static int ensure(cgnn_ctx* ctx, DevBuf& b, size_t bytes) {
+    if (bytes <= b.cap) return 0;
+    if (b.p) { CU(cudaFree(b.p)); b.p = nullptr; b.cap = 0; }
+    size_t cap = std::max<size_t>(bytes, 256);
+    CU(cudaMalloc(&b.p, cap));
+    b.cap = cap;
+    return 0;
+}
+
+static bool is_device_ptr(const void* p) {
+    cudaPointerAttributes a{};
+    if (cudaPointerGetAttributes(&a, p) != cudaSuccess) { cudaGetLastError(); return false; }
+    return a.type == cudaMemoryTypeDevice || a.type == cudaMemoryTypeManaged;
+}
+
+// Make `bytes` of caller memory available on the device: returns the caller's pointer if it is
+// already device memory, else stages it through `b`.
+static int stage_in(cgnn_ctx* ctx, DevBuf& b, const void* src, size_t bytes, const void** out) {
+    if (!src) { *out = nullptr; return 0; }
+    if (is_device_ptr(src)) { *out = src; return 0; }
+    int rc = ensure(ctx, b, bytes);
+    if (rc) return rc;
+    CU(cudaMemcpyAsync(b.p, src, bytes, cudaMemcpyHostToDevice, ctx->stream));
+    *out = b.p;
+    return 0;
+}
+
+// Device-side landing buffer for an output: the caller's own pointer if it is device memory.
+static int stage_out(cgnn_ctx* ctx, DevBuf& b, void* dst, size_t bytes, void** out) {
+    if (!dst) { *out = nullptr; return 0; }
+    if (is_device_ptr(dst)) { *out = dst; return 0; }
+    int rc = ensure(ctx, b, bytes);
+    if (rc) return rc;
+    *out = b.p;
+    return 0;
+}
+
+static int copy_back(cgnn_ctx* ctx, void* dst, const void* dev, size_t bytes) {
+    if (!dst || dst == dev) return 0;
+    CU(cudaMemcpyAsync(dst, dev, bytes, cudaMemcpyDeviceToHost, ctx->stream));
+    return 0;
+}
+
+static int check_hp(cgnn_ctx* ctx, const cgnn_hparams* hp) {
+    if (!hp) return fail(ctx, CGNN_ERR_ARG, "hparams is NULL");
+    if (hp->h_layer_dim < 1 || hp->h_layer_dim > CGNN_MAX_H)
+        return fail(ctx, CGNN_ERR_LIMIT, "h_layer_dim=%d outside [1,%d]", hp->h_layer_dim, CGNN_MAX_H);
+    if (hp->train_epochs < 0 || hp->test_epochs < 0) return fail(ctx, CGNN_ERR_ARG, "negative epoch count");
+    if (hp->exp_policy < 0 || hp->exp_policy > 1) return fail(ctx, CGNN_ERR_ARG, "exp_policy=%d unknown", hp->exp_policy);
+    return 0;
+}
+
+template <int POL>
+static cudaError_t launch_pairwise(const PairwiseArgs& a, int grid, size_t smem, cudaStream_t st) {
+    cudaError_t e = cudaFuncSetAttribute(pairwise_kernel<POL>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem));
+    if (e != cudaSuccess) return e;
+    pairwise_kernel<POL><<<grid, PW_NT, smem, st>>>(a);
+    return cudaGetLastError();
+}
+
+static int pairwise_occupancy(int pol, size_t smem) {
+    int n = 0;
+    cudaError_t e;
+    if (pol == 0) {
+        cudaFuncSetAttribute(pairwise_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem));
+        e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, pairwise_kernel<0>, PW_NT, smem);
+    } else {
+        cudaFuncSetAttribute(pairwise_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem));
+        e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, pairwise_kernel<1>, PW_NT, smem);
+    }
+    if (e != cudaSuccess) { cudaGetLastError(); return 0; }
+    return n;
+}
+
+// ---------------------------------------------------------------------------------------------
+extern "C" {
+
+int cgnn_b200_version(void) { return CGNN_B200_VERSION; }
+
+int cgnn_b200_create(cgnn_ctx** out, int device_id) {
+    if (!out) return CGNN_ERR_ARG;
+    *out = nullptr;
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess || n == 0) { cudaGetLastError(); return CGNN_ERR_NODEVICE; }
+    if (device_id < 0 || device_id >= n) return CGNN_ERR_ARG;
+    cgnn_ctx* ctx = new cgnn_ctx();
+    ctx->device = device_id;
+    if (cudaSetDevice(device_id) != cudaSuccess || cudaGetDeviceProperties(&ctx->prop, device_id) != cudaSuccess) {
+        cudaGetLastError();
+        delete ctx;
+        return CGNN_ERR_CUDA;
+    }
+    if (ctx->prop.major != 10) {   // the library carries sm_100a code only: fail loudly, never fall back
+        delete ctx;
+        return CGNN_ERR_NODEVICE;
+    }
+    if (cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking) != cudaSuccess ||
+        cudaEventCreate(&ctx->ev0) != cudaSuccess || cudaEventCreate(&ctx->ev1) != cudaSuccess) {
+        cudaGetLastError();
+        delete ctx;
+        return CGNN_ERR_CUDA;
+    }
+    *out = ctx;
+    return CGNN_OK;
+}
+
+void cgnn_b200_destroy(cgnn_ctx* ctx) {
+    if (!ctx) return;
+    cudaSetDevice(ctx->device);
+    DevBuf* bufs[] = {&ctx->xy, &ctx->nrows, &ctx->inst, &ctx->scores, &ctx->noise, &ctx->init, &ctx->trace,
+                      &ctx->pout, &ctx->counter, &ctx->dbg[0], &ctx->dbg[1], &ctx->dbg[2], &ctx->dbg[3], &ctx->dbg[4]};
+    for (DevBuf* b : bufs)
+        if (b->p) cudaFree(b->p);
+    if (ctx->ev0) cudaEventDestroy(ctx->ev0);
+    if (ctx->ev1) cudaEventDestroy(ctx->ev1);
+    if (ctx->own_stream && ctx->stream) cudaStreamDestroy(ctx->stream);
+    delete ctx;
+}
+
+const char* cgnn_b200_last_error(const cgnn_ctx* ctx) { return ctx ? ctx->err.c_str() : "null context"; }
+
+int cgnn_b200_set_stream(cgnn_ctx* ctx, void* stream) {
+    if (!ctx) return CGNN_ERR_ARG;
+    if (ctx->own_stream && ctx->stream) cudaStreamDestroy(ctx->stream);
+    ctx->stream = static_cast<cudaStream_t>(stream);
+    ctx->own_stream = false;
+    return CGNN_OK;
+}
+
+float cgnn_b200_last_kernel_ms(const cgnn_ctx* ctx) { return ctx ? ctx->last_ms : -1.f; }
+int cgnn_b200_last_launch_count(const cgnn_ctx* ctx) { return ctx ? ctx->last_launches : 0; }
+
+int cgnn_b200_device_info(const cgnn_ctx* ctx, int* n_sm, int* ctas_per_sm_pairwise) {
+    if (!ctx) return CGNN_ERR_ARG;
+    if (n_sm) *n_sm = ctx->prop.multiProcessorCount;
+    if (ctas_per_sm_pairwise) *ctas_per_sm_pairwise = ctx->pw_ctas_per_sm;
+    return CGNN_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
+static int run_pairwise_impl(cgnn_ctx* ctx, const cgnn_hparams* hp, const float* xy, const int* n_rows, int n_pairs,
+                             int ld_rows, int n_runs, unsigned long long uid_base, const float* noise,
+                             const float* init_params, float* scores, float* loss_trace, float* params_out,
+                             float* const dbg_host[5], int dbg_steps) {
+    if (!ctx) return CGNN_ERR_ARG;
+    ctx->err.clear();
+    int rc = check_hp(ctx, hp);
+    if (rc) return rc;
+    if (!xy || !n_rows) return fail(ctx, CGNN_ERR_ARG, "xy / n_rows is NULL");
+    if (n_pairs < 1 || n_runs < 1 || ld_rows < 1) return fail(ctx, CGNN_ERR_ARG, "n_pairs, n_runs, ld_rows must be >= 1");
+    if (!scores && !dbg_host) return fail(ctx, CGNN_ERR_ARG, "scores is NULL");
+    CU(cudaSetDevice(ctx->device));
+
+    // n_rows on the host (tiny)
+    std::vector<int> nr(n_pairs);
+    if (is_device_ptr(n_rows)) CU(cudaMemcpy(nr.data(), n_rows, sizeof(int) * n_pairs, cudaMemcpyDeviceToHost));
+    else std::memcpy(nr.data(), n_rows, sizeof(int) * n_pairs);
+    int max_n = 0;
+    for (int p = 0; p < n_pairs; ++p) {
+        if (nr[p] < 1 || nr[p] > ld_rows) return fail(ctx, CGNN_ERR_ARG, "n_rows[%d]=%d outside [1, ld_rows=%d]", p, nr[p], ld_rows);
+        if (nr[p] > CGNN_MAX_ROWS_PAIRWISE || nr[p] > PW_MAX_ROWS)
+            return fail(ctx, CGNN_ERR_LIMIT, "n_rows[%d]=%d exceeds CGNN_MAX_ROWS_PAIRWISE=%d (subsample first, GNN.py:150-153)",
+                        p, nr[p], CGNN_MAX_ROWS_PAIRWISE);
+        max_n = std::max(max_n, nr[p]);
+    }
+    const long long n_inst_ll = 2LL * n_pairs * n_runs;
+    if (n_inst_ll > (1LL << 30)) return fail(ctx, CGNN_ERR_LIMIT, "too many instances in one batch");
+    const int n_inst = dbg_host ? 1 : int(n_inst_ll);   // the parity probe runs (pair 0, run 0, direction 0) only
+    const int h = hp->h_layer_dim, P = 4 * h + 1;
+    const int epochs = hp->train_epochs + hp->test_epochs;
+
+    // instance table, longest first (cost ~ N^2), so the tail of the persistent queue is short
+    std::vector<int> order(n_pairs);
+    std::iota(order.begin(), order.end(), 0);
+    std::stable_sort(order.begin(), order.end(), [&](int a, int b) { return nr[a] > nr[b]; });
+    std::vector<int4> tab;
+    tab.reserve(n_inst);
+    for (int p : order)
+        for (int r = 0; r < n_runs; ++r)
+            for (int d = 0; d < 2; ++d) tab.push_back(make_int4(p, r, d, (p * n_runs + r) * 2 + d));
+    tab.resize(n_inst);
+
+    PairwiseArgs a{};
+    const void* dp = nullptr;
+    void* op = nullptr;
+    if ((rc = stage_in(ctx, ctx->xy, xy, sizeof(float) * 2 * size_t(n_pairs) * ld_rows, &dp))) return rc;
+    a.xy = static_cast<const float*>(dp);
+    if ((rc = ensure(ctx, ctx->nrows, sizeof(int) * n_pairs))) return rc;
+    CU(cudaMemcpyAsync(ctx->nrows.p, nr.data(), sizeof(int) * n_pairs, cudaMemcpyHostToDevice, ctx->stream));
+    a.n_rows = static_cast<const int*>(ctx->nrows.p);
+    if ((rc = ensure(ctx, ctx->inst, sizeof(int4) * n_inst))) return rc;
+    CU(cudaMemcpyAsync(ctx->inst.p, tab.data(), sizeof(int4) * n_inst, cudaMemcpyHostToDevice, ctx->stream));
+    a.inst = static_cast<const int4*>(ctx->inst.p);
+    if ((rc = stage_in(ctx, ctx->noise, noise, sizeof(float) * size_t(n_inst) * epochs * ld_rows, &dp))) return rc;
+    a.noise = static_cast<const float*>(dp);
+    if ((rc = stage_in(ctx, ctx->init, init_params, sizeof(float) * size_t(n_inst) * P, &dp))) return rc;
+    a.init_params = static_cast<const float*>(dp);
+    if ((rc = stage_out(ctx, ctx->scores, scores, sizeof(float) * n_inst, &op))) return rc;
+    a.scores = static_cast<float*>(op);
+    if ((rc = stage_out(ctx, ctx->trace, loss_trace, sizeof(float) * size_t(n_inst) * epochs, &op))) return rc;
+    a.trace = static_cast<float*>(op);
+    if ((rc = stage_out(ctx, ctx->pout, params_out, sizeof(float) * size_t(n_inst) * P, &op))) return rc;
+    a.params_out = static_cast<float*>(op);
+    if ((rc = ensure(ctx, ctx->counter, 256))) return rc;
+    a.counter = static_cast<int*>(ctx->counter.p);
+    CU(cudaMemsetAsync(a.counter, 0, 256, ctx->stream));
+
+    size_t dbg_bytes[5] = {0, 0, 0, 0, 0};
+    float* dbg_dev[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
+    if (dbg_host) {
+        const size_t N0 = size_t(nr[0]);
+        dbg_bytes[0] = sizeof(float) * dbg_steps;
+        dbg_bytes[1] = dbg_bytes[2] = sizeof(float) * dbg_steps * N0;
+        dbg_bytes[3] = dbg_bytes[4] = sizeof(float) * dbg_steps * size_t(P);
+        for (int k = 0; k < 5; ++k) {
+            if ((rc = stage_out(ctx, ctx->dbg[k], dbg_host[k], dbg_bytes[k], &op))) return rc;
+            dbg_dev[k] = static_cast<float*>(op);
+        }
+        a.dbg_loss = dbg_dev[0]; a.dbg_yhat = dbg_dev[1]; a.dbg_dldy = dbg_dev[2];
+        a.dbg_grad = dbg_dev[3]; a.dbg_params = dbg_dev[4];
+    }
+
+    a.n_inst = n_inst; a.ld_rows = ld_rows; a.np_max = 32 * ((max_n + 31) / 32);
+    a.h = h; a.train_epochs = hp->train_epochs; a.test_epochs = hp->test_epochs; a.trace_every = hp->trace_every;
+    a.lr = hp->learning_rate; a.init_std = hp->init_std;
+    a.key = make_uint2((unsigned int)(hp->seed & 0xffffffffu),
+                       (unsigned int)(hp->seed >> 32) ^ (unsigned int)(uid_base >> 32));
+    a.uid_base = (unsigned int)(uid_base & 0xffffffffu);
+
+    const size_t smem = pw_smem_bytes(a.np_max, h);
+    if (smem > size_t(ctx->prop.sharedMemPerBlockOptin))
+        return fail(ctx, CGNN_ERR_LIMIT, "instance needs %zu B of shared memory, device allows %zu", smem,
+                    size_t(ctx->prop.sharedMemPerBlockOptin));
+    int per_sm = pairwise_occupancy(hp->exp_policy, smem);
+    if (per_sm < 1) return fail(ctx, CGNN_ERR_CUDA, "pairwise kernel cannot be resident (smem %zu B)", smem);
+    ctx->pw_ctas_per_sm = per_sm;
+    const int grid = std::min(n_inst, per_sm * ctx->prop.multiProcessorCount);
+
+    CU(cudaEventRecord(ctx->ev0, ctx->stream));
+    cudaError_t le = hp->exp_policy == 0 ? launch_pairwise<0>(a, grid, smem, ctx->stream)
+                                         : launch_pairwise<1>(a, grid, smem, ctx->stream);
+    if (le != cudaSuccess) return fail(ctx, CGNN_ERR_CUDA, "pairwise kernel launch: %s", cudaGetErrorString(le));
+    CU(cudaEventRecord(ctx->ev1, ctx->stream));
+    ctx->last_launches = 1;
+
+    if ((rc = copy_back(ctx, scores, a.scores, sizeof(float) * n_inst))) return rc;
+    if ((rc = copy_back(ctx, loss_trace, a.trace, sizeof(float) * size_t(n_inst) * epochs))) return rc;
+    if ((rc = copy_back(ctx, params_out, a.params_out, sizeof(float) * size_t(n_inst) * P))) return rc;
+    if (dbg_host)
+        for (int k = 0; k < 5; ++k)
+            if ((rc = copy_back(ctx, dbg_host[k], dbg_dev[k], dbg_bytes[k]))) return rc;
+    CU(cudaStreamSynchronize(ctx->stream));
+    CU(cudaEventElapsedTime(&ctx->last_ms, ctx->ev0, ctx->ev1));
+    return CGNN_OK;
+}
+
+int cgnn_b200_run_pairwise(cgnn_ctx* ctx, const cgnn_hparams* hp, const float* xy, const int* n_rows, int n_pairs,
+                           int ld_rows, int n_runs, unsigned long long uid_base, const float* noise,
+                           const float* init_params, float* scores, float* loss_trace, float* params_out) {
+    return run_pairwise_impl(ctx, hp, xy, n_rows, n_pairs, ld_rows, n_runs, uid_base, noise, init_params, scores,
+                             loss_trace, params_out, nullptr, 0);
+}
+
+int cgnn_b200_pairwise_step_debug(cgnn_ctx* ctx, const cgnn_hparams* hp, const float* xy, int n_rows, int n_steps,
+                                  const float* noise, const float* init_params, float* out_loss, float* out_yhat,
+                                  float* out_dldy, float* out_grad, float* out_params) {
+    if (!ctx) return CGNN_ERR_ARG;
+    if (!hp) return fail(ctx, CGNN_ERR_ARG, "hparams is NULL");
+    if (!noise || !init_params) return fail(ctx, CGNN_ERR_ARG, "step_debug needs caller-supplied noise and parameters");
+    if (n_steps < 1) return fail(ctx, CGNN_ERR_ARG, "n_steps must be >= 1");
+    cgnn_hparams h2 = *hp;
+    h2.train_epochs = n_steps;
+    h2.test_epochs = 0;
+    h2.trace_every = 0;
+    float* dbg[5] = {out_loss, out_yhat, out_dldy, out_grad, out_params};
+    return run_pairwise_impl(ctx, &h2, xy, &n_rows, 1, n_rows, 1, 0ULL, noise, init_params, nullptr, nullptr, nullptr, dbg,
+                             n_steps);
+}
+
+
+int cgnn_b200_probe_peak(cgnn_ctx* ctx, int kind, int reps, double* out_per_second) {
+    if (!ctx || !out_per_second) return CGNN_ERR_ARG;
+    if (kind < 0 || kind > 1) return fail(ctx, CGNN_ERR_ARG, "probe kind %d unknown", kind);
+    CU(cudaSetDevice(ctx->device));
+    int rc = ensure(ctx, ctx->counter, 256);
+    if (rc) return rc;
+    const int iters = 4096, grid = ctx->prop.multiProcessorCount * 4, nt = 512;
+    double best = 0.0;
+    for (int r = 0; r < std::max(reps, 1) + 1; ++r) {      // first launch is a warm-up
+        CU(cudaEventRecord(ctx->ev0, ctx->stream));
+        if (kind == 0) probe_mufu_kernel<<<grid, nt, 0, ctx->stream>>>(static_cast<float*>(ctx->counter.p), iters);
+        else           probe_ffma_kernel<<<grid, nt, 0, ctx->stream>>>(static_cast<float*>(ctx->counter.p), iters);
+        CU(cudaGetLastError());
+        CU(cudaEventRecord(ctx->ev1, ctx->stream));
+        CU(cudaStreamSynchronize(ctx->stream));
+        float ms = 0.f;
+        CU(cudaEventElapsedTime(&ms, ctx->ev0, ctx->ev1));
+        const double ops = double(grid) * nt * double(iters) * 8.0 * (kind == 0 ? 1.0 : 2.0);
+        if (r > 0) best = std::max(best, ops / (double(ms) * 1e-3));
+    }
+    *out_per_second = best;
+    return CGNN_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,149 @@
+// Shared device helpers of the cgnn_b200 engine (sm_100a).
+//
+// Reference math: Code/cgnn/utils/Loss.py:10-32 (MMD), GNN.py:21-29 (init), GNN.py:64 (noise),
+// tf.train.AdamOptimizer (TF-1 "epsilon hat" Adam).  See DESIGN.md for the block form used here.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace cgnn {
+
+// ---------------------------------------------------------------------------------------------
+// Bandwidths (Loss.py:10).  Fixed at compile time exactly as in the reference, so that the
+// multiplies by gamma become FFMA/FMUL immediates and the x2 / x4 ratios can be exploited.
+// ---------------------------------------------------------------------------------------------
+#define CGNN_LOG2E 1.4426950408889634f
+constexpr float G0 = 0.005f, G1 = 0.05f, G2 = 0.25f, G3 = 0.5f, G4 = 1.0f, G5 = 5.0f, G6 = 50.0f;
+constexpr float C0 = -G0 * CGNN_LOG2E, C1 = -G1 * CGNN_LOG2E, C2 = -G2 * CGNN_LOG2E, C3 = -G3 * CGNN_LOG2E,
+                C4 = -G4 * CGNN_LOG2E, C5 = -G5 * CGNN_LOG2E, C6 = -G6 * CGNN_LOG2E;
+constexpr float SUM_GAMMA_KERNELS_AT_ZERO = 7.0f;   // sum_g exp(0)
+
+__device__ __forceinline__ float ex2f(float x) {        // one MUFU.EX2, flush-to-zero: no range fix-up code
+    float y;
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+    return y;
+}
+
+// The seven kernel values exp(-gamma_g * D) of one pair evaluation.
+//   POL 0: seven MUFU ex2.
+//   POL 1: five MUFU ex2; gamma=0.5 and gamma=1 are the square and 4th power of the gamma=0.25 value
+//          (bandwidth ratios are exactly 2, so this is exact up to 2 / 4 x the ex2 rounding error).
+template <int POL>
+struct KernelVals {
+    float k0, k1, k2, k3, k4, k5, k6;
+    __device__ __forceinline__ explicit KernelVals(float D) {
+        k0 = ex2f(D * C0);
+        k1 = ex2f(D * C1);
+        k2 = ex2f(D * C2);
+        if (POL == 0) {
+            k3 = ex2f(D * C3);
+            k4 = ex2f(D * C4);
+        } else {
+            k3 = k2 * k2;
+            k4 = k3 * k3;
+        }
+        k5 = ex2f(D * C5);
+        k6 = ex2f(D * C6);
+    }
+    // sum_g k_g      (loss)
+    __device__ __forceinline__ float sum() const { return ((k0 + k1) + (k2 + k3)) + ((k4 + k5) + k6); }
+    // sum_g gamma_g k_g   (gradient weight; the common factor 4/N^2 is applied once per row later)
+    __device__ __forceinline__ float wsum() const {
+        float a = fmaf(G1, k1, G0 * k0);
+        float b = fmaf(G3, k3, G2 * k2);
+        float c = fmaf(G5, k5, k4);           // G4 == 1
+        a = fmaf(G6, k6, a);
+        return (a + b) + c;
+    }
+};
+
+// ---------------------------------------------------------------------------------------------
+// Philox4x32-10 counter RNG + Box-Muller.  Engine-defined streams (the reference is unseeded):
+//   key     = (seed_lo, seed_hi)
+//   counter = (index, step, stream, instance uid)     -> 4 x 32 random bits -> 4 normals
+// Restated in numpy in tests/philox_np.py to check the in-kernel generator.
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ uint4 philox4x32_10(uint4 c, uint2 k) {
+    const uint32_t M0 = 0xD2511F53u, M1 = 0xCD9E8D57u, W0 = 0x9E3779B9u, W1 = 0xBB67AE85u;
+#pragma unroll
+    for (int r = 0; r < 10; ++r) {
+        uint32_t hi0 = __umulhi(M0, c.x), lo0 = M0 * c.x;
+        uint32_t hi1 = __umulhi(M1, c.z), lo1 = M1 * c.z;
+        c = make_uint4(hi1 ^ c.y ^ k.x, lo1, hi0 ^ c.w ^ k.y, lo0);
+        k.x += W0;
+        k.y += W1;
+    }
+    return c;
+}
+
+__device__ __forceinline__ float u01(uint32_t r) {     // (0,1), exact in fp32
+    return (float(r >> 9) + 0.5f) * (1.0f / 8388608.0f);
+}
+
+__device__ __forceinline__ float4 normal4(uint4 r) {
+    float4 n;
+    float r0 = sqrtf(-2.0f * logf(u01(r.x)));
+    float r1 = sqrtf(-2.0f * logf(u01(r.z)));
+    float s0, c0, s1, c1;
+    sincospif(2.0f * u01(r.y), &s0, &c0);
+    sincospif(2.0f * u01(r.w), &s1, &c1);
+    n.x = r0 * c0; n.y = r0 * s0; n.z = r1 * c1; n.w = r1 * s1;
+    return n;
+}
+
+enum : uint32_t { STREAM_NOISE = 0u, STREAM_INIT = 1u };
+
+// ---------------------------------------------------------------------------------------------
+// Order-independent accumulation into shared memory: 64-bit fixed point (2^-36 resolution,
+// +-2^27 range) with native integer atomics.  Integer addition is associative, so the result does
+// not depend on warp scheduling: the engine is bit-reproducible run to run.
+// ---------------------------------------------------------------------------------------------
+#define CGNN_FX_SCALE   68719476736.0            /* 2^36 */
+#define CGNN_FX_INV     (1.0 / 68719476736.0)
+
+__device__ __forceinline__ void fx_add(long long* p, double v) {
+    long long q = __double2ll_rn(v * CGNN_FX_SCALE);
+    atomicAdd(reinterpret_cast<unsigned long long*>(p), static_cast<unsigned long long>(q));
+}
+__device__ __forceinline__ double fx_get(const long long* p) { return double(*p) * CGNN_FX_INV; }
+
+// ---------------------------------------------------------------------------------------------
+// Warp reductions
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ double warp_sum(double v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+
+// Transposing reduction: every lane brings 32 partial sums v[0..31]; on return lane l holds the
+// warp-wide total of v[l].  31 shuffles instead of 32 x 5.
+__device__ __forceinline__ float warp_reduce32(float (&v)[32], int lane) {
+#pragma unroll
+    for (int ofs = 16, n = 32; ofs >= 1; ofs >>= 1, n >>= 1) {
+        const bool up = (lane & ofs) != 0;
+#pragma unroll
+        for (int i = 0; i < n / 2; ++i) {
+            float send = up ? v[i] : v[i + n / 2];
+            float keep = up ? v[i + n / 2] : v[i];
+            v[i] = keep + __shfl_xor_sync(0xffffffffu, send, ofs);
+        }
+    }
+    return v[0];
+}
+
+// ---------------------------------------------------------------------------------------------
+// TF-1 Adam, fp32, one parameter per call.  lr_t = lr*sqrt(1-b2^t)/(1-b1^t) is computed by the caller.
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ float adam_update(float theta, float g, float& m, float& v, float lr_t) {
+    m = 0.9f * m + 0.1f * g;                         // (1-beta1) rounds to 0.1f in fp32 as in TF
+    v = 0.999f * v + 0.001f * g * g;
+    return theta - lr_t * m / (sqrtf(v) + 1e-8f);
+}
+
+}  // namespace cgnn

@@ -1,0 +1,152 @@
+"""Host-side handle on the CUDA engine: one `Engine` = one cgnn_ctx = one GPU.
+
+This is the batched replacement of the reference's per-instance scorers
+(`tf_run_instance`, Code/cgnn/GNN.py:135-166; `run_CGNN_tf`, CGNN.py:163-195;
+`run_CGNN_confounders_tf`, CGNN_confounders.py:182-216).  It only marshals buffers
+across the C ABI (include/cgnn_b200.h); all arithmetic happens in the CUDA kernels.
+There is no CPU path: constructing an Engine without the built library or without an
+sm_100 GPU raises.
+"""
+import ctypes as C
+
+import numpy as np
+
+from . import _lib
+from .utils.Settings import SETTINGS
+
+
+class EngineError(RuntimeError):
+    pass
+
+
+def _ptr(a):
+    """Raw address of a numpy array (host) or torch tensor (host or device); None -> NULL."""
+    if a is None:
+        return None
+    if isinstance(a, np.ndarray):
+        return C.c_void_p(a.ctypes.data)
+    return C.c_void_p(a.data_ptr())          # torch.Tensor
+
+
+def _is_torch(a):
+    return a is not None and not isinstance(a, np.ndarray) and hasattr(a, "data_ptr")
+
+
+def make_hparams(**kw):
+    """cgnn_hparams from SETTINGS with the reference's kwargs-override rule
+    (GNN.py:45-48,90,112; CGNN.py:48-51,115,137): the same names, per call."""
+    hp = _lib.Hparams()
+    hp.h_layer_dim = int(kw.get("h_layer_dim", SETTINGS.h_layer_dim))
+    hp.train_epochs = int(kw.get("train_epochs", SETTINGS.train_epochs))
+    hp.test_epochs = int(kw.get("test_epochs", SETTINGS.test_epochs))
+    hp.learning_rate = float(kw.get("learning_rate", SETTINGS.learning_rate))
+    hp.init_std = float(kw.get("init_std", SETTINGS.init_weights))
+    hp.exp_policy = int(kw.get("exp_policy", SETTINGS.exp_policy))
+    hp.trace_every = int(kw.get("trace_every", 0))
+    hp.seed = int(kw.get("seed", SETTINGS.seed)) & 0xFFFFFFFFFFFFFFFF
+    return hp
+
+
+class Engine:
+    def __init__(self, device=0):
+        self._lib = _lib.load()
+        h = C.c_void_p()
+        rc = self._lib.cgnn_b200_create(C.byref(h), int(device))
+        if rc != 0:
+            raise EngineError("cgnn_b200_create(device=%d) failed with status %d "
+                              "(no sm_100 GPU? this engine has no CPU fallback)" % (device, rc))
+        self._h = h
+        self.device = int(device)
+
+    def close(self):
+        if getattr(self, "_h", None):
+            self._lib.cgnn_b200_destroy(self._h)
+            self._h = None
+
+    __del__ = close
+
+    def _check(self, rc, what):
+        if rc != 0:
+            msg = self._lib.cgnn_b200_last_error(self._h)
+            raise EngineError("%s failed (%d): %s" % (what, rc, msg.decode() if msg else ""))
+
+    # -- info -------------------------------------------------------------------------------
+    @property
+    def last_kernel_ms(self):
+        return float(self._lib.cgnn_b200_last_kernel_ms(self._h))
+
+    @property
+    def last_launch_count(self):
+        return int(self._lib.cgnn_b200_last_launch_count(self._h))
+
+    def device_info(self):
+        a, b = C.c_int(), C.c_int()
+        self._check(self._lib.cgnn_b200_device_info(self._h, C.byref(a), C.byref(b)), "device_info")
+        return dict(n_sm=a.value, ctas_per_sm_pairwise=b.value)
+
+    def set_stream(self, cuda_stream_ptr):
+        self._check(self._lib.cgnn_b200_set_stream(self._h, C.c_void_p(cuda_stream_ptr)), "set_stream")
+
+    def probe_peak(self, kind, reps=5):
+        """kind 'mufu' -> exp/s, 'ffma' -> flop/s of this chip's pipes (micro-benchmark)."""
+        out = C.c_double()
+        k = {"mufu": 0, "ffma": 1}[kind]
+        self._check(self._lib.cgnn_b200_probe_peak(self._h, k, reps, C.byref(out)), "probe_peak")
+        return out.value
+
+    # -- pairwise ---------------------------------------------------------------------------
+    def run_pairwise(self, xy, n_rows=None, n_runs=None, uid_base=0, noise=None, init_params=None,
+                     want_trace=False, want_params=False, scores_out=None, **kw):
+        """Score every (pair, run, direction) instance.
+
+        xy: [n_pairs, ld_rows, 2] float32, numpy (host) or torch (host/cuda) - column 0 = A.
+        Returns dict(scores [n_pairs, n_runs, 2], trace?, params?) as numpy arrays, or writes the
+        scores into `scores_out` (e.g. a cuda tensor) when given.
+        """
+        hp = make_hparams(**kw)
+        n_runs = int(n_runs if n_runs is not None else kw.get("nb_runs", SETTINGS.NB_RUNS))
+        if isinstance(xy, np.ndarray):
+            xy = np.ascontiguousarray(xy, dtype=np.float32)
+        n_pairs, ld_rows = int(xy.shape[0]), int(xy.shape[1])
+        if tuple(xy.shape[2:]) != (2,):
+            raise ValueError("xy must be [n_pairs, rows, 2]")
+        if n_rows is None:
+            n_rows = np.full(n_pairs, ld_rows, np.int32)
+        n_rows = np.ascontiguousarray(n_rows, dtype=np.int32)
+        n_inst = n_pairs * n_runs * 2
+        P = 4 * hp.h_layer_dim + 1
+        epochs = hp.train_epochs + hp.test_epochs
+        if noise is not None and isinstance(noise, np.ndarray):
+            noise = np.ascontiguousarray(noise, np.float32)
+            if noise.size != n_inst * epochs * ld_rows:
+                raise ValueError("noise must be [n_inst, train+test epochs, ld_rows]")
+        if init_params is not None and isinstance(init_params, np.ndarray):
+            init_params = np.ascontiguousarray(init_params, np.float32)
+            if init_params.size != n_inst * P:
+                raise ValueError("init_params must be [n_inst, 4h+1]")
+        scores = scores_out if scores_out is not None else np.empty((n_pairs, n_runs, 2), np.float32)
+        trace = np.empty((n_inst, epochs), np.float32) if want_trace else None
+        pout = np.empty((n_inst, P), np.float32) if want_params else None
+        rc = self._lib.cgnn_b200_run_pairwise(self._h, C.byref(hp), _ptr(xy), _ptr(n_rows), n_pairs, ld_rows,
+                                              n_runs, C.c_ulonglong(int(uid_base)), _ptr(noise), _ptr(init_params),
+                                              _ptr(scores), _ptr(trace), _ptr(pout))
+        self._check(rc, "cgnn_b200_run_pairwise")
+        return dict(scores=scores, trace=trace, params=pout)
+
+    def pairwise_step_debug(self, xy, noise, init_params, **kw):
+        """Parity probe: consecutive train steps of ONE instance (column 0 = cause)."""
+        hp = make_hparams(**kw)
+        xy = np.ascontiguousarray(xy, np.float32)
+        noise = np.ascontiguousarray(noise, np.float32)
+        init_params = np.ascontiguousarray(init_params, np.float32)
+        n_rows, n_steps = xy.shape[0], noise.shape[0]
+        P = 4 * hp.h_layer_dim + 1
+        assert noise.shape == (n_steps, n_rows) and init_params.shape == (P,)
+        out = dict(loss=np.empty(n_steps, np.float32), yhat=np.empty((n_steps, n_rows), np.float32),
+                   dldy=np.empty((n_steps, n_rows), np.float32), grad=np.empty((n_steps, P), np.float32),
+                   params=np.empty((n_steps, P), np.float32))
+        rc = self._lib.cgnn_b200_pairwise_step_debug(self._h, C.byref(hp), _ptr(xy), n_rows, n_steps, _ptr(noise),
+                                                     _ptr(init_params), _ptr(out["loss"]), _ptr(out["yhat"]),
+                                                     _ptr(out["dldy"]), _ptr(out["grad"]), _ptr(out["params"]))
+        self._check(rc, "cgnn_b200_pairwise_step_debug")
+        return out

@@ -1,0 +1,136 @@
+/* cgnn_b200 - C ABI of the B200-native CGNN hot-path engine.
+ *
+ * The reference (CaoAo/CGNN) has no native code: its seam for this path is a Python
+ * function pointer selected by a backend string,
+ *     backend_alg_dic = {"TensorFlow": tf_run_instance}        Code/cgnn/GNN.py:182,193
+ *     self.infer_graph = run_CGNN_tf                           Code/cgnn/CGNN.py:344-345
+ *     self.infer_graph = run_CGNN_confounders_tf               Code/cgnn/CGNN_confounders.py:475-476
+ * called once per (pair | candidate graph, run) through joblib.  One call per instance cannot
+ * fill 148 SMs, so the replacement boundary is BATCHED: one call scores every
+ * (pair | graph, run[, direction]) instance of a batch.  Each entry point below names the
+ * reference function(s) it replaces.  Plain C types only; no exceptions cross the boundary;
+ * every function returns 0 on success or a negative cgnn_status, and the message for the
+ * last failure on a context is available from cgnn_b200_last_error().
+ *
+ * Ownership: the caller owns every buffer passed in; buffers may be host memory (pageable or
+ * pinned) or device memory on the context's device (detected with cudaPointerGetAttributes).
+ * Calls are synchronous (results are in the caller's buffer on return).  A context is not
+ * re-entrant: one call at a time per context; separate contexts are independent.
+ * NaN/Inf scores are returned as they are, never masked (the reference filters them in the
+ * graph paths only, CGNN.py:217,240 - that stays the caller's job).
+ */
+#ifndef CGNN_B200_H
+#define CGNN_B200_H
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define CGNN_B200_VERSION      100      /* major*10000 + minor*100 + patch */
+#define CGNN_N_GAMMAS          7        /* Loss.py:10 - fixed at compile time, like the reference */
+#define CGNN_MAX_ROWS_PAIRWISE 2048     /* reference subsamples to SETTINGS.max_nb_points = 1500 (GNN.py:150-153) */
+#define CGNN_MAX_H             64       /* hidden width limit (reference default 20, scripts use 30) */
+
+typedef enum cgnn_status {
+    CGNN_OK            =  0,
+    CGNN_ERR_ARG       = -1,   /* bad argument (null pointer, size out of range ...) */
+    CGNN_ERR_CUDA      = -2,   /* a CUDA runtime call failed; see last_error */
+    CGNN_ERR_NOMEM     = -3,   /* device allocation failed */
+    CGNN_ERR_LIMIT     = -4,   /* problem exceeds an engine limit (rows, hidden width, inputs) */
+    CGNN_ERR_NODEVICE  = -5    /* no usable sm_100 device */
+} cgnn_status;
+
+typedef struct cgnn_ctx cgnn_ctx;
+
+/* Hyper-parameters.  Mirrors the knobs of Code/cgnn/utils/Settings.py:26-41 that reach the
+ * device code, plus the engine's own (seed, exp_policy, trace_every). */
+typedef struct cgnn_hparams {
+    int   h_layer_dim;        /* SETTINGS.h_layer_dim (Settings.py:36) */
+    int   train_epochs;       /* SETTINGS.train_epochs (Settings.py:37) */
+    int   test_epochs;        /* SETTINGS.test_epochs  (Settings.py:38) */
+    float learning_rate;      /* SETTINGS.learning_rate (Settings.py:31) */
+    float init_std;           /* SETTINGS.init_weights  (Settings.py:32) */
+    int   exp_policy;         /* how the 7 Gaussian kernels of one pair evaluation are produced:
+                                 0 = seven MUFU ex2;  1 = five MUFU ex2, gamma 0.5 and 1 by squaring gamma 0.25 */
+    int   trace_every;        /* >0: also compute the (pre-update) training loss on every trace_every-th
+                                 train step into loss_trace (GNN.py:98-102 prints every 100th); 0 = never */
+    int   reserved0;
+    unsigned long long seed;  /* engine Philox seed.  The reference is unseeded (no hit for "seed" in its tree). */
+} cgnn_hparams;
+
+/* ---- life cycle ------------------------------------------------------------------------- */
+
+int  cgnn_b200_version(void);
+
+/* Creates a context bound to ONE device (one process per GPU is the multi-GPU model; the
+ * reference's "/gpu:(offset + run % nb_gpu)" placement, GNN.py:159, becomes the caller's
+ * sharding of instances over contexts).  Replaces GNN_tf.__init__'s session creation
+ * (GNN.py:77-80) - done once, not once per instance. */
+int  cgnn_b200_create(cgnn_ctx** out, int device_id);
+void cgnn_b200_destroy(cgnn_ctx* ctx);
+const char* cgnn_b200_last_error(const cgnn_ctx* ctx);   /* owned by ctx; valid until the next call on ctx */
+
+/* Run the engine's kernels on an existing CUDA stream (e.g. torch's current stream) instead
+ * of the context's own.  stream is a cudaStream_t passed as void*. */
+int  cgnn_b200_set_stream(cgnn_ctx* ctx, void* stream);
+
+/* Device time (ms, CUDA events on the launching stream) of the main kernel of the last
+ * run_* call on this context; number of kernels that call launched. */
+float cgnn_b200_last_kernel_ms(const cgnn_ctx* ctx);
+int   cgnn_b200_last_launch_count(const cgnn_ctx* ctx);
+
+/* ---- pairwise GNN ----------------------------------------------------------------------- */
+
+/* Scores every (pair, run, direction) instance of a batch of cause-effect pairs.
+ * Replaces tf_run_instance + tf_evalcausalscore_pairwise + GNN_tf.{__init__,train,evaluate}
+ * (Code/cgnn/GNN.py:135-166, 129-132, 33-126) for all runs of all pairs at once.
+ *
+ *   xy            [n_pairs][ld_rows][2] fp32, column 0 = A, column 1 = B (already standardised and,
+ *                 if needed, subsampled by the caller as GNN.py:150-153 does)
+ *   n_rows        [n_pairs] valid rows of each pair, 1 <= n_rows[p] <= min(ld_rows, CGNN_MAX_ROWS_PAIRWISE)
+ *   n_runs        SETTINGS.NB_RUNS
+ *   uid_base      global index of this batch's first instance: instance (pair p, run r, direction d)
+ *                 draws its random numbers from Philox stream uid_base + (p*n_runs + r)*2 + d, so
+ *                 results do not depend on how a sweep is cut into batches or sharded over GPUs
+ *   noise         NULL (in-kernel Philox N(0,1)) or [n_inst][train_epochs+test_epochs][ld_rows] fp32:
+ *                 the e of GNN.py:64 for every sess.run, supplied by the caller (parity mode)
+ *   init_params   NULL (in-kernel N(0, init_std^2), GNN.py:21-29) or [n_inst][4h+1] fp32, layout
+ *                 [W_in row X (h) | W_in row e (h) | b_in (h) | W_out (h) | b_out]
+ *   scores        out [n_pairs][n_runs][2]: mean test MMD of A->B (d=0) and B->A (d=1)  (GNN.py:161-163)
+ *   loss_trace    NULL or out [n_inst][train_epochs+test_epochs]: training losses on traced steps
+ *                 (NaN elsewhere) followed by every evaluation loss
+ *   params_out    NULL or out [n_inst][4h+1]: parameters after training
+ * with n_inst = n_pairs*n_runs*2 and instance index (p*n_runs + r)*2 + d. */
+int  cgnn_b200_run_pairwise(cgnn_ctx* ctx, const cgnn_hparams* hp,
+                            const float* xy, const int* n_rows, int n_pairs, int ld_rows, int n_runs,
+                            unsigned long long uid_base,
+                            const float* noise, const float* init_params,
+                            float* scores, float* loss_trace, float* params_out);
+
+/* Parity probe: n_steps consecutive TRAIN steps of one pairwise instance (column 0 of xy = cause)
+ * with caller-supplied parameters and noise, dumping what the reference's graph would hold at
+ * each sess.run (GNN.py:93-96): the loss before the update, the generated column, dLoss/d out_y,
+ * the parameter gradient and the parameters after the Adam update.  Runs the production kernel.
+ *   xy [n_rows][2], noise [n_steps][n_rows], init_params [4h+1]
+ *   out_loss [n_steps], out_yhat [n_steps][n_rows], out_dldy [n_steps][n_rows],
+ *   out_grad [n_steps][4h+1], out_params [n_steps][4h+1]    (any of them may be NULL) */
+int  cgnn_b200_pairwise_step_debug(cgnn_ctx* ctx, const cgnn_hparams* hp,
+                                   const float* xy, int n_rows, int n_steps,
+                                   const float* noise, const float* init_params,
+                                   float* out_loss, float* out_yhat, float* out_dldy,
+                                   float* out_grad, float* out_params);
+
+/* ---- measurement support ---------------------------------------------------------------- */
+
+/* Micro-benchmarks that measure this chip's own pipe peaks (MEASURED_PEAKS.json holds only HBM
+ * and bf16 tensor numbers): kind 0 = MUFU ex2.approx.ftz.f32 (result in exp/s),
+ * kind 1 = FP32 FFMA (result in flop/s, 2 per FFMA).  Best of `reps` launches. */
+int  cgnn_b200_probe_peak(cgnn_ctx* ctx, int kind, int reps, double* out_per_second);
+
+/* Number of SMs of the context's device and persistent CTAs per SM the engine launches. */
+int  cgnn_b200_device_info(const cgnn_ctx* ctx, int* n_sm, int* ctas_per_sm_pairwise);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* CGNN_B200_H */
