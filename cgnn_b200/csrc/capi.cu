@@ -130,7 +130,7 @@ static int check_hp(cgnn_ctx* ctx, const cgnn_hparams* hp) {
     if (hp->h_layer_dim < 1 || hp->h_layer_dim > CGNN_MAX_H)
         return fail(ctx, CGNN_ERR_LIMIT, "h_layer_dim=%d outside [1,%d]", hp->h_layer_dim, CGNN_MAX_H);
     if (hp->train_epochs < 0 || hp->test_epochs < 0) return fail(ctx, CGNN_ERR_ARG, "negative epoch count");
-    if (hp->exp_policy < 0 || hp->exp_policy > 1) return fail(ctx, CGNN_ERR_ARG, "exp_policy=%d unknown", hp->exp_policy);
+    if (hp->exp_policy < 0 || hp->exp_policy > 3) return fail(ctx, CGNN_ERR_ARG, "exp_policy=%d unknown", hp->exp_policy);
     return 0;
 }
 
@@ -145,13 +145,13 @@ static cudaError_t launch_pairwise(const PairwiseArgs& a, int grid, size_t smem,
 static int pairwise_occupancy(int pol, size_t smem) {
     int n = 0;
     cudaError_t e;
-    if (pol == 0) {
-        cudaFuncSetAttribute(pairwise_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem));
-        e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, pairwise_kernel<0>, PW_NT, smem);
-    } else {
-        cudaFuncSetAttribute(pairwise_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem));
-        e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, pairwise_kernel<1>, PW_NT, smem);
-    }
+#define OCC(P_)                                                                                              \
+    case P_:                                                                                                 \
+        cudaFuncSetAttribute(pairwise_kernel<P_>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem));   \
+        e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, pairwise_kernel<P_>, PW_NT, smem);             \
+        break;
+    switch (pol) { OCC(0) OCC(1) OCC(2) OCC(3) default: e = cudaErrorInvalidValue; }
+#undef OCC
     if (e != cudaSuccess) { cudaGetLastError(); return 0; }
     return n;
 }
@@ -321,8 +321,13 @@ static int run_pairwise_impl(cgnn_ctx* ctx, const cgnn_hparams* hp, const float*
     const int grid = std::min(n_inst, per_sm * ctx->prop.multiProcessorCount);
 
     CU(cudaEventRecord(ctx->ev0, ctx->stream));
-    cudaError_t le = hp->exp_policy == 0 ? launch_pairwise<0>(a, grid, smem, ctx->stream)
-                                         : launch_pairwise<1>(a, grid, smem, ctx->stream);
+    cudaError_t le = cudaErrorInvalidValue;
+    switch (hp->exp_policy) {
+        case 0: le = launch_pairwise<0>(a, grid, smem, ctx->stream); break;
+        case 1: le = launch_pairwise<1>(a, grid, smem, ctx->stream); break;
+        case 2: le = launch_pairwise<2>(a, grid, smem, ctx->stream); break;
+        case 3: le = launch_pairwise<3>(a, grid, smem, ctx->stream); break;
+    }
     if (le != cudaSuccess) return fail(ctx, CGNN_ERR_CUDA, "pairwise kernel launch: %s", cudaGetErrorString(le));
     CU(cudaEventRecord(ctx->ev1, ctx->stream));
     ctx->last_launches = 1;

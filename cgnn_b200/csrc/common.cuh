@@ -24,38 +24,58 @@ __device__ __forceinline__ float ex2f(float x) {        // one MUFU.EX2, flush-t
     return y;
 }
 
-// The seven kernel values exp(-gamma_g * D) of one pair evaluation.
-//   POL 0: seven MUFU ex2.
-//   POL 1: five MUFU ex2; gamma=0.5 and gamma=1 are the square and 4th power of the gamma=0.25 value
-//          (bandwidth ratios are exactly 2, so this is exact up to 2 / 4 x the ex2 rounding error).
+// The seven kernel values exp(-gamma_g * D) of one pair evaluation, reduced on the fly to
+//   ksum = sum_g k_g          (loss)            wsum = sum_g gamma_g k_g   (gradient weight)
+// Policies (hparams.exp_policy) trade MUFU ex2 for FP32 multiplies using the exact ratios of the
+// bandwidth list (Loss.py:10): 0.25 -> 0.5 -> 1 are squarings, 0.005 -> 0.05 is a 10th power,
+// 1 -> 5 a 5th power.  A power p multiplies the relative error of the ex2 it starts from by p.
+//   POL 0: 7 MUFU                                          (reference-like: every kernel its own exp)
+//   POL 1: 5 MUFU   gamma 0.5, 1 from 0.25                 (error x2, x4)
+//   POL 2: 4 MUFU   + gamma 0.05 from 0.005                (error x10)
+//   POL 3: 3 MUFU   + gamma 5 from 1                       (error x20 relative to the 0.25 ex2)
 template <int POL>
-struct KernelVals {
-    float k0, k1, k2, k3, k4, k5, k6;
-    __device__ __forceinline__ explicit KernelVals(float D) {
-        k0 = ex2f(D * C0);
-        k1 = ex2f(D * C1);
-        k2 = ex2f(D * C2);
-        if (POL == 0) {
-            k3 = ex2f(D * C3);
-            k4 = ex2f(D * C4);
-        } else {
-            k3 = k2 * k2;
-            k4 = k3 * k3;
-        }
-        k5 = ex2f(D * C5);
-        k6 = ex2f(D * C6);
-    }
-    // sum_g k_g      (loss)
-    __device__ __forceinline__ float sum() const { return ((k0 + k1) + (k2 + k3)) + ((k4 + k5) + k6); }
-    // sum_g gamma_g k_g   (gradient weight; the common factor 4/N^2 is applied once per row later)
-    __device__ __forceinline__ float wsum() const {
+__device__ __forceinline__ float pow10f(float k) { float a = k * k; float b = a * a; float c = b * k; return c * c; }
+
+template <int POL>
+__device__ __forceinline__ float wsum(float D) {
+    const float k0 = ex2f(D * C0);
+    const float k1 = (POL >= 2) ? pow10f<POL>(k0) : ex2f(D * C1);
+    const float k2 = ex2f(D * C2);
+    const float k6 = ex2f(D * C6);
+    if (POL == 0) {
+        const float k3 = ex2f(D * C3), k4 = ex2f(D * C4), k5 = ex2f(D * C5);
         float a = fmaf(G1, k1, G0 * k0);
         float b = fmaf(G3, k3, G2 * k2);
         float c = fmaf(G5, k5, k4);           // G4 == 1
         a = fmaf(G6, k6, a);
         return (a + b) + c;
+    } else {
+        const float k3 = k2 * k2;                         // gamma 0.5
+        float k5;
+        if (POL >= 3) { const float k4 = k3 * k3; const float a = k4 * k4; k5 = (a * a) * k4; }
+        else k5 = ex2f(D * C5);
+        // G2 k2 + G3 k2^2 + G4 k2^4 by Horner in k2 (k4 is never formed explicitly)
+        float t = fmaf(G4, k3, G3);
+        t = fmaf(t, k2, G2);
+        float w = t * k2;
+        float u = fmaf(G1, k1, G0 * k0);
+        w = fmaf(G5, k5, w);
+        u = fmaf(G6, k6, u);
+        return w + u;
     }
-};
+}
+
+template <int POL>
+__device__ __forceinline__ float ksum(float D) {
+    const float k0 = ex2f(D * C0);
+    const float k1 = (POL >= 2) ? pow10f<POL>(k0) : ex2f(D * C1);
+    const float k2 = ex2f(D * C2);
+    const float k6 = ex2f(D * C6);
+    float k3, k4, k5;
+    if (POL == 0) { k3 = ex2f(D * C3); k4 = ex2f(D * C4); } else { k3 = k2 * k2; k4 = k3 * k3; }
+    if (POL >= 3) { const float a = k4 * k4; k5 = (a * a) * k4; } else k5 = ex2f(D * C5);
+    return ((k0 + k1) + (k2 + k3)) + ((k4 + k5) + k6);
+}
 
 // ---------------------------------------------------------------------------------------------
 // Philox4x32-10 counter RNG + Box-Muller.  Engine-defined streams (the reference is unseeded):

@@ -70,7 +70,7 @@ __host__ __device__ inline size_t pw_smem_bytes(int np_max, int h) {
     b += size_t(np_max) * 4;                     // es
     b += size_t(Pp) * 4 * 3;                     // theta, m, v
     b += size_t(PW_NW) * (nchunk * 32 + 4) * 4;  // per-warp partial gradient sums
-    b += size_t(PW_NW + 2) * 8;                  // red[], TT
+    b += size_t(PW_NW + 4) * 8;                  // red[], TT, beta1^t, beta2^t, lr_t
     return (b + 15) & ~size_t(15);
 }
 
@@ -92,7 +92,7 @@ __device__ __forceinline__ float bc_train(float xi, float yi, const float2* __re
         const float2 c = col[j];
         const float dx = xi - c.x, dy = yi - c.y;
         const float D = fmaf(dy, dy, dx * dx);
-        acc = fmaf(KernelVals<POL>(D).wsum(), dy, acc);
+        acc = fmaf(wsum<POL>(D), dy, acc);
     }
     return acc;
 }
@@ -106,7 +106,7 @@ __device__ __forceinline__ float bc_eval(float xi, float yi, const float2* __res
         const float2 c = col[j];
         const float dx = xi - c.x, dy = yi - c.y;
         const float D = fmaf(dy, dy, dx * dx);
-        acc += KernelVals<POL>(D).sum();
+        acc += ksum<POL>(D);
     }
     return acc;
 }
@@ -123,7 +123,7 @@ __device__ __forceinline__ float pp_sym_train(float xi, float yi, const float2* 
         const float2 c = Pc[J0 + ((lane + s) & 31)];
         const float dx = xi - c.x, dy = yi - c.y;
         const float D = fmaf(dy, dy, dx * dx);
-        const float t = KernelVals<POL>(D).wsum() * dy;
+        const float t = wsum<POL>(D) * dy;
         ra += t;
         ca += t;
         ca = __shfl_sync(0xffffffffu, ca, src);
@@ -298,7 +298,7 @@ __global__ void __launch_bounds__(PW_NT, PW_MIN_CTAS) pairwise_kernel(const Pair
         s.Tc = reinterpret_cast<float2*>(p);      p += size_t(a.np_max) * 8;
         s.Pc = reinterpret_cast<float2*>(p);      p += size_t(a.np_max) * 8;
         s.g64 = reinterpret_cast<long long*>(p);  p += size_t(a.np_max) * 8;
-        s.red = reinterpret_cast<double*>(p);     p += size_t(PW_NW + 2) * 8;
+        s.red = reinterpret_cast<double*>(p);     p += size_t(PW_NW + 4) * 8;
         s.es = reinterpret_cast<float*>(p);       p += size_t(a.np_max) * 4;
         s.theta = reinterpret_cast<float*>(p);    p += size_t(Pp) * 4;
         s.am = reinterpret_cast<float*>(p);       p += size_t(Pp) * 4;
@@ -354,12 +354,19 @@ __global__ void __launch_bounds__(PW_NT, PW_MIN_CTAS) pairwise_kernel(const Pair
             const double tt = block_sum(part, s.red, warp, lane);
             if (tid == 0) s_TT = tt;
         }
-        float b1p = 1.f, b2p = 1.f;              // beta^t accumulators, as TF keeps them
+        // beta^t accumulators.  TF keeps them in fp32, which puts a 6e-6 relative error on every step size
+        // ((1 - 0.999f^t) inherits fp32(0.999)'s rounding); thread 0 keeps them in fp64 in shared memory.
+        if (tid == 0) { s.red[PW_NW + 1] = 1.0; s.red[PW_NW + 2] = 1.0; }
         const double invN2 = 1.0 / (double(N) * double(N));
 
         // ---- training (GNN.py:92-96) --------------------------------------------------------
         for (int it = 0; it < a.train_epochs; ++it) {
             __syncthreads();
+            if (tid == 0) {   // lr_t of this step (read after three more barriers)
+                const double b1p = s.red[PW_NW + 1] * 0.9, b2p = s.red[PW_NW + 2] * 0.999;
+                s.red[PW_NW + 1] = b1p; s.red[PW_NW + 2] = b2p;
+                s.red[PW_NW + 3] = double(a.lr) * sqrt(1.0 - b2p) / (1.0 - b1p);
+            }
             pw_forward(s, a, N, h, it, uid, noise ? noise + size_t(it) * a.ld_rows : nullptr, tid);
             __syncthreads();
             const bool traced = a.dbg_loss || (a.trace && a.trace_every > 0 && it % a.trace_every == 0);
@@ -383,13 +390,12 @@ __global__ void __launch_bounds__(PW_NT, PW_MIN_CTAS) pairwise_kernel(const Pair
             }
             pw_backward_partials(s, N, h, tid, warp, lane);
             __syncthreads();
-            b1p *= 0.9f; b2p *= 0.999f;
             if (tid < P) {
                 const int slot = pw_slot(tid, h);
                 float g = 0.f;
 #pragma unroll
                 for (int w = 0; w < PW_NW; ++w) g += s.part[w * s.part_stride + slot];
-                const float lr_t = a.lr * sqrtf(1.f - b2p) / (1.f - b1p);
+                const float lr_t = float(s.red[PW_NW + 3]);
                 float m = s.am[tid], v = s.av[tid];
                 const float th = adam_update(s.theta[tid], g, m, v, lr_t);
                 s.am[tid] = m; s.av[tid] = v; s.theta[tid] = th;

@@ -28,7 +28,7 @@ def _oracle_train(xy, noise, theta0, h, lr=0.01):
     return {k: np.array(v) for k, v in out.items()}
 
 
-@pytest.mark.parametrize("pol", [0, 1])
+@pytest.mark.parametrize("pol", [0, 1, 2, 3])
 @pytest.mark.parametrize("n,h", [(257, 30), (64, 20), (96, 7), (33, 64), (1, 5), (2, 8), (31, 20), (32, 20)])
 def test_step_debug_matches_oracle(engine, n, h, pol):
     rng = np.random.default_rng(100 + n)
@@ -45,7 +45,7 @@ def test_step_debug_matches_oracle(engine, n, h, pol):
         assert relerr(got["params"][s], ref["params"][s]) < TOL
 
 
-@pytest.mark.parametrize("pol", [0, 1])
+@pytest.mark.parametrize("pol", [0, 1, 2, 3])
 def test_step_debug_full_size(engine, pol):
     """N = 1500 (SETTINGS.max_nb_points), h = 30 (run_GNN_pairwise_inference.py:9)."""
     n, h = 1500, 30
@@ -62,7 +62,7 @@ def test_step_debug_full_size(engine, pol):
         assert relerr(got["params"][s], ref["params"][s]) < TOL
 
 
-@pytest.mark.parametrize("pol", [0, 1])
+@pytest.mark.parametrize("pol", [0, 1, 2, 3])
 def test_trained_state_parity(engine, pol):
     """After 150 Adam steps the loss is ~1e-2 and made of cancelling O(1) block sums: the hard case."""
     from oracle import gnn as og
