@@ -392,3 +392,122 @@ int cgnn_b200_probe_peak(cgnn_ctx* ctx, int kind, int reps, double* out_per_seco
 }
 
 }  // extern "C"
+
+// =============================================================================================
+// Entry point for callers that cannot allocate device memory (see include/cgnn_b200.h).
+//
+// Everything the pairwise launch needs beyond the caller's own input and output buffers - the
+// work-queue head, the per-pair row counts and the instance table - lives in ONE statically
+// allocated device array.  It is part of the library image: every GPU that loads the library
+// carries these bytes until the process exits, whether or not this entry point is ever called.
+// =============================================================================================
+#define CGNN_NOALLOC_MAX_PAIRS      1024
+#define CGNN_NOALLOC_MAX_INSTANCES  8192
+
+struct NoAllocScratch {
+    int  counter[64];                            // work-queue head (+ padding to 256 B); must be 0 at launch
+    int  n_rows[CGNN_NOALLOC_MAX_PAIRS];
+    int4 inst[CGNN_NOALLOC_MAX_INSTANCES];       // (pair, run, direction, output index)
+};
+static_assert(sizeof(NoAllocScratch) == 256 + 4 * CGNN_NOALLOC_MAX_PAIRS + 16 * CGNN_NOALLOC_MAX_INSTANCES, "layout");
+
+static __device__ __align__(256) unsigned char g_noalloc_scratch[sizeof(NoAllocScratch)];   // 135,424 bytes
+
+// Fills the scratch for one call.  Device code may name the array directly.
+__global__ void noalloc_setup_kernel(int n_pairs, int n_rows, int n_runs) {
+    NoAllocScratch* s = reinterpret_cast<NoAllocScratch*>(g_noalloc_scratch);
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < 64) s->counter[i] = 0;               // the array keeps the previous call's contents: re-zero the queue head
+    if (i < n_pairs) s->n_rows[i] = n_rows;
+    if (i < 2 * n_pairs * n_runs) {
+        const int d = i & 1, pr = i >> 1;
+        s->inst[i] = make_int4(pr / n_runs, pr % n_runs, d, i);
+    }
+}
+
+// Device address of the array, per device.  In host code the name `g_noalloc_scratch` is only a
+// handle for the runtime, not a device address, so it is resolved once per device (with that
+// device current) and the resulting pointer is what the kernels receive.
+static void* g_noalloc_addr[64] = {nullptr};
+
+static int na_fail(char* buf, int len, int code, const char* fmt, ...) {
+    if (buf && len > 0) {
+        va_list ap;
+        va_start(ap, fmt);
+        vsnprintf(buf, size_t(len), fmt, ap);
+        va_end(ap);
+    }
+    return code;
+}
+
+#define NA_CU(call)                                                                                      \
+    do {                                                                                                 \
+        cudaError_t e_ = (call);                                                                         \
+        if (e_ != cudaSuccess) return na_fail(errbuf, errbuf_len, CGNN_ERR_CUDA, "%s: %s", #call, cudaGetErrorString(e_)); \
+    } while (0)
+
+extern "C" int cgnn_b200_run_pairwise_noalloc(int device, void* stream, const cgnn_hparams* hp, const float* d_xy,
+                                               int n_pairs, int n_rows, int n_runs, unsigned long long uid_base,
+                                               float* d_scores, char* errbuf, int errbuf_len) {
+    if (errbuf && errbuf_len > 0) errbuf[0] = 0;
+    if (!hp || !d_xy || !d_scores) return na_fail(errbuf, errbuf_len, CGNN_ERR_ARG, "hparams, d_xy and d_scores must not be NULL");
+    if (hp->h_layer_dim < 1 || hp->h_layer_dim > CGNN_MAX_H)
+        return na_fail(errbuf, errbuf_len, CGNN_ERR_LIMIT, "h_layer_dim=%d outside [1,%d]", hp->h_layer_dim, CGNN_MAX_H);
+    if (hp->train_epochs < 0 || hp->test_epochs < 0 || hp->exp_policy < 0 || hp->exp_policy > 3)
+        return na_fail(errbuf, errbuf_len, CGNN_ERR_ARG, "bad epoch count or exp_policy");
+    if (n_pairs < 1 || n_runs < 1 || n_rows < 1) return na_fail(errbuf, errbuf_len, CGNN_ERR_ARG, "n_pairs, n_runs, n_rows must be >= 1");
+    if (n_rows > CGNN_MAX_ROWS_PAIRWISE)
+        return na_fail(errbuf, errbuf_len, CGNN_ERR_LIMIT, "n_rows=%d exceeds CGNN_MAX_ROWS_PAIRWISE=%d", n_rows, CGNN_MAX_ROWS_PAIRWISE);
+    if (n_pairs > CGNN_NOALLOC_MAX_PAIRS || 2LL * n_pairs * n_runs > CGNN_NOALLOC_MAX_INSTANCES)
+        return na_fail(errbuf, errbuf_len, CGNN_ERR_LIMIT,
+                       "batch of %d pairs x %d runs x 2 directions exceeds the static scratch (max %d pairs, %d instances): "
+                       "split the batch or use cgnn_b200_run_pairwise", n_pairs, n_runs, CGNN_NOALLOC_MAX_PAIRS,
+                       CGNN_NOALLOC_MAX_INSTANCES);
+    if (device < 0 || device >= 64) return na_fail(errbuf, errbuf_len, CGNN_ERR_ARG, "device %d outside [0,64)", device);
+    NA_CU(cudaSetDevice(device));
+    if (!is_device_ptr(d_xy) || !is_device_ptr(d_scores))
+        return na_fail(errbuf, errbuf_len, CGNN_ERR_ARG, "d_xy and d_scores must be device memory (staging host buffers would need an allocation)");
+    int cc_major = 0, n_sm = 0, smem_optin = 0;
+    NA_CU(cudaDeviceGetAttribute(&cc_major, cudaDevAttrComputeCapabilityMajor, device));
+    NA_CU(cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, device));
+    NA_CU(cudaDeviceGetAttribute(&smem_optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, device));
+    if (cc_major != 10) return na_fail(errbuf, errbuf_len, CGNN_ERR_NODEVICE, "device %d is not sm_100", device);
+
+    // one-time set-up on this device: resolve the device address of the static array
+    if (!g_noalloc_addr[device]) {
+        void* p = nullptr;
+        NA_CU(cudaGetSymbolAddress(&p, g_noalloc_scratch));
+        g_noalloc_addr[device] = p;
+    }
+    NoAllocScratch* sc = static_cast<NoAllocScratch*>(g_noalloc_addr[device]);
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    const int n_inst = 2 * n_pairs * n_runs;
+
+    noalloc_setup_kernel<<<(std::max(n_inst, 64) + 255) / 256, 256, 0, st>>>(n_pairs, n_rows, n_runs);
+    NA_CU(cudaGetLastError());
+
+    PairwiseArgs a{};
+    a.xy = d_xy; a.n_rows = sc->n_rows; a.inst = sc->inst; a.counter = sc->counter;
+    a.n_inst = n_inst; a.ld_rows = n_rows; a.np_max = 32 * ((n_rows + 31) / 32);
+    a.h = hp->h_layer_dim; a.train_epochs = hp->train_epochs; a.test_epochs = hp->test_epochs; a.trace_every = 0;
+    a.lr = hp->learning_rate; a.init_std = hp->init_std;
+    a.key = make_uint2((unsigned int)(hp->seed & 0xffffffffu), (unsigned int)(hp->seed >> 32) ^ (unsigned int)(uid_base >> 32));
+    a.uid_base = (unsigned int)(uid_base & 0xffffffffu);
+    a.scores = d_scores;
+
+    const size_t smem = pw_smem_bytes(a.np_max, a.h);
+    if (smem > size_t(smem_optin)) return na_fail(errbuf, errbuf_len, CGNN_ERR_LIMIT, "instance needs %zu B of shared memory", smem);
+    const int per_sm = pairwise_occupancy(hp->exp_policy, smem);
+    if (per_sm < 1) return na_fail(errbuf, errbuf_len, CGNN_ERR_CUDA, "pairwise kernel cannot be resident");
+    const int grid = std::min(n_inst, per_sm * n_sm);
+    cudaError_t le = cudaErrorInvalidValue;
+    switch (hp->exp_policy) {
+        case 0: le = launch_pairwise<0>(a, grid, smem, st); break;
+        case 1: le = launch_pairwise<1>(a, grid, smem, st); break;
+        case 2: le = launch_pairwise<2>(a, grid, smem, st); break;
+        case 3: le = launch_pairwise<3>(a, grid, smem, st); break;
+    }
+    if (le != cudaSuccess) return na_fail(errbuf, errbuf_len, CGNN_ERR_CUDA, "pairwise kernel launch: %s", cudaGetErrorString(le));
+    NA_CU(cudaStreamSynchronize(st));
+    return CGNN_OK;
+}

@@ -120,6 +120,44 @@ int  cgnn_b200_pairwise_step_debug(cgnn_ctx* ctx, const cgnn_hparams* hp,
                                    float* out_loss, float* out_yhat, float* out_dldy,
                                    float* out_grad, float* out_params);
 
+/* ---- pairwise GNN for callers that must not allocate device memory ------------------------ */
+
+/* No counterpart in the reference: this entry point exists only in this library.
+ *
+ * cgnn_b200_run_pairwise() grows staging buffers with cudaMalloc when a batch is larger than any
+ * seen before.  Some hosts cannot afford that: a service whose device memory has been handed over
+ * in full to another framework's pool (cudaMalloc would fail or evict), a loop with a latency
+ * budget (cudaMalloc synchronises the device and may take milliseconds), or a process that freezes
+ * its memory map after start-up.  For them this variant scores a batch with NO allocation of any
+ * kind: no cudaMalloc/cudaFree, no context object, no host heap.  It is the same instance kernel;
+ * the scratch it needs besides your buffers (work-queue head, row counts, instance table) is a
+ * fixed 135,424-byte array compiled into the library, resident on every GPU that loads the
+ * library for as long as the process lives.
+ *
+ * Limits (CGNN_ERR_LIMIT with a message otherwise): n_pairs <= 1024 and n_pairs*n_runs*2 <= 8192
+ * instances per call; all pairs have the same n_rows (<= CGNN_MAX_ROWS_PAIRWISE).  Split larger
+ * sweeps into several calls (advance uid_base by n_pairs*n_runs*2 each time).
+ *
+ *   device, stream  CUDA device ordinal and a cudaStream_t on it (as void*, NULL = default stream)
+ *   d_xy            DEVICE memory, [n_pairs][n_rows][2] fp32, column 0 = A (see cgnn_b200_run_pairwise)
+ *   d_scores        DEVICE memory, out [n_pairs][n_runs][2]
+ *   errbuf          caller-owned buffer (may be NULL) that receives the message of a failure
+ * Noise and initial parameters always come from the in-kernel Philox streams (seed, uid_base), so
+ * the scores are bit-identical to cgnn_b200_run_pairwise() with noise = init_params = NULL.
+ *
+ * Things to know:
+ *  - The first call on each device resolves the device address of the static array
+ *    (cudaGetSymbolAddress) and loads the kernels; make that first call during start-up, before
+ *    any stream capture begins.
+ *  - The array is shared by every call in the process and keeps the previous call's contents; each
+ *    call re-initialises the parts that must start from zero on `stream` before its main launch.
+ *    Two calls whose GPU work overlaps (different streams or threads) race on it: serialise them.
+ *  - Synchronous like the other entry points: returns after `stream` has drained. */
+int  cgnn_b200_run_pairwise_noalloc(int device, void* stream, const cgnn_hparams* hp,
+                                    const float* d_xy, int n_pairs, int n_rows, int n_runs,
+                                    unsigned long long uid_base, float* d_scores,
+                                    char* errbuf, int errbuf_len);
+
 /* ---- measurement support ---------------------------------------------------------------- */
 
 /* Micro-benchmarks that measure this chip's own pipe peaks (MEASURED_PEAKS.json holds only HBM
