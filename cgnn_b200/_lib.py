@@ -13,6 +13,12 @@ class Hparams(C.Structure):
                 ("trace_every", C.c_int), ("reserved0", C.c_int), ("seed", C.c_ulonglong)]
 
 
+class GraphBatchStruct(C.Structure):
+    _fields_ = [("n_graphs", C.c_int), ("n_var", C.c_int), ("n_noise_cols", C.c_int),
+                ("node_col", C.POINTER(C.c_int)), ("n_parents", C.POINTER(C.c_int)), ("n_inputs", C.POINTER(C.c_int)),
+                ("in_ptr", C.POINTER(C.c_int)), ("in_idx", C.POINTER(C.c_int))]
+
+
 _F = C.POINTER(C.c_float)
 _I = C.POINTER(C.c_int)
 _V = C.c_void_p
@@ -31,6 +37,10 @@ SYMBOLS = {
                                          C.c_ulonglong, _V, _V, _V, _V, _V]),
     "cgnn_b200_pairwise_step_debug": (C.c_int, [_V, C.POINTER(Hparams), _V, C.c_int, C.c_int, _V, _V,
                                                 _V, _V, _V, _V, _V]),
+    "cgnn_b200_run_graph": (C.c_int, [_V, C.POINTER(Hparams), _V, C.c_int, C.POINTER(GraphBatchStruct), C.c_int, _V, C.c_int,
+                                      C.c_ulonglong, _V, _V, C.c_int, _V, _V, _V]),
+    "cgnn_b200_graph_step_debug": (C.c_int, [_V, C.POINTER(Hparams), _V, C.c_int, C.POINTER(GraphBatchStruct), C.c_int, _V, _V,
+                                             C.c_int, _V, _V, _V, _V, _V]),
     "cgnn_b200_probe_peak": (C.c_int, [_V, C.c_int, C.c_int, C.POINTER(C.c_double)]),
     "cgnn_b200_run_pairwise_noalloc": (C.c_int, [C.c_int, _V, C.POINTER(Hparams), _V, C.c_int, C.c_int, C.c_int,
                                                  C.c_ulonglong, _V, C.c_char_p, C.c_int]),

@@ -1,18 +1,28 @@
 """Builds libcgnn_b200.so in-tree with nvcc for sm_100a (no JIT cache, no torch extension).
 
 The shared library is the product; it is built here (cross-compiled, no GPU needed) and travels
-to the GPU box with the repository snapshot.
+to the GPU box with the repository snapshot.  Translation units are compiled in parallel:
+capi.cu (pairwise path, life cycle, probes), graph_api.cu (graph path host side) and graph_inst.cu
+once per padded column count (-DCGNN_DP=8|16|20|24|32).
 """
 import os
 import shutil
 import subprocess
+from concurrent.futures import ThreadPoolExecutor
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
+OBJ = os.path.join(HERE, "build")
 LIB = os.path.join(HERE, "libcgnn_b200.so")
-SOURCES = ["capi.cu"]
+GRAPH_DPS = (8, 16, 20, 24, 32)
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
-              "-Xcompiler", "-fPIC", "-shared"]
+              "-Xcompiler", "-fPIC"]
+
+
+def _units():
+    u = [("capi", "capi.cu", []), ("graph_api", "graph_api.cu", [])]
+    u += [("graph_dp%d" % d, "graph_inst.cu", ["-DCGNN_DP=%d" % d]) for d in GRAPH_DPS]
+    return u
 
 
 def _nvcc():
@@ -22,26 +32,37 @@ def _nvcc():
     return exe
 
 
-def _stale():
-    if not os.path.exists(LIB):
-        return True
-    t = os.path.getmtime(LIB)
+def _deps_mtime():
     deps = [os.path.join(CSRC, f) for f in os.listdir(CSRC)]
     deps.append(os.path.join(HERE, "..", "include", "cgnn_b200.h"))
-    return any(os.path.getmtime(d) > t for d in deps if os.path.exists(d))
+    return max(os.path.getmtime(d) for d in deps if os.path.exists(d))
 
 
 def build_library(force=False, verbose=False):
     """Compile the CUDA sources into cgnn_b200/libcgnn_b200.so; returns its path."""
-    if not force and not _stale():
+    if not force and os.path.exists(LIB) and os.path.getmtime(LIB) >= _deps_mtime():
         return LIB
-    cmd = [_nvcc()] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + \
-          ["-o", LIB] + [os.path.join(CSRC, s) for s in SOURCES]
-    r = subprocess.run(cmd, capture_output=True, text=True)
+    os.makedirs(OBJ, exist_ok=True)
+    nvcc = _nvcc()
+    logs = []
+
+    def compile_one(unit):
+        name, src, defs = unit
+        obj = os.path.join(OBJ, name + ".o")
+        cmd = [nvcc] + NVCC_FLAGS + defs + (["-Xptxas", "-v"] if verbose else []) + ["-c", os.path.join(CSRC, src), "-o", obj]
+        r = subprocess.run(cmd, capture_output=True, text=True)
+        if r.returncode != 0:
+            raise RuntimeError("nvcc failed on %s:\n%s%s" % (src, r.stdout, r.stderr))
+        logs.append("== %s\n%s" % (name, r.stderr))
+        return obj
+
+    with ThreadPoolExecutor(max_workers=min(8, os.cpu_count() or 1)) as ex:
+        objs = list(ex.map(compile_one, _units()))
+    r = subprocess.run([nvcc, "-shared", "-o", LIB] + objs, capture_output=True, text=True)
     if r.returncode != 0:
-        raise RuntimeError("nvcc failed:\n" + r.stdout + r.stderr)
+        raise RuntimeError("link failed:\n" + r.stdout + r.stderr)
     if verbose:
-        print(r.stderr)
+        print("\n".join(logs))
     return LIB
 
 

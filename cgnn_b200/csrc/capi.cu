@@ -9,7 +9,7 @@
 #include <string>
 #include <vector>
 
-#include "../../include/cgnn_b200.h"
+#include "ctx.h"
 #include "pairwise.cuh"
 
 using namespace cgnn;
@@ -42,96 +42,6 @@ __global__ void __launch_bounds__(512) probe_ffma_kernel(float* sink, int iters)
 #pragma unroll
     for (int k = 0; k < 8; ++k) s += x[k];
     if (s == 123.456f) sink[0] = s;
-}
-
-// ---------------------------------------------------------------------------------------------
-struct DevBuf {
-    void* p = nullptr;
-    size_t cap = 0;
-};
-
-struct cgnn_ctx {
-    int device = 0;
-    cudaStream_t stream = nullptr;
-    bool own_stream = true;
-    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
-    cudaDeviceProp prop{};
-    std::string err;
-    float last_ms = 0.f;
-    int last_launches = 0;
-    int pw_ctas_per_sm = 0;
-    // staging buffers (grow-only)
-    DevBuf xy, nrows, inst, scores, noise, init, trace, pout, counter, dbg[5];
-};
-
-static int fail(cgnn_ctx* c, int code, const char* fmt, ...) {
-    char buf[512];
-    va_list ap;
-    va_start(ap, fmt);
-    vsnprintf(buf, sizeof buf, fmt, ap);
-    va_end(ap);
-    if (c) c->err = buf;
-    return code;
-}
-
-#define CU(call)                                                                                         \
-    do {                                                                                                 \
-        cudaError_t e_ = (call);                                                                         \
-        if (e_ != cudaSuccess)                                                                           \
-            return fail(ctx, e_ == cudaErrorMemoryAllocation ? CGNN_ERR_NOMEM : CGNN_ERR_CUDA, "%s: %s", \
-                        #call, cudaGetErrorString(e_));                                                  \
-    } while (0)
-
-static int ensure(cgnn_ctx* ctx, DevBuf& b, size_t bytes) {
-    if (bytes <= b.cap) return 0;
-    if (b.p) { CU(cudaFree(b.p)); b.p = nullptr; b.cap = 0; }
-    size_t cap = std::max<size_t>(bytes, 256);
-    CU(cudaMalloc(&b.p, cap));
-    b.cap = cap;
-    return 0;
-}
-
-static bool is_device_ptr(const void* p) {
-    cudaPointerAttributes a{};
-    if (cudaPointerGetAttributes(&a, p) != cudaSuccess) { cudaGetLastError(); return false; }
-    return a.type == cudaMemoryTypeDevice || a.type == cudaMemoryTypeManaged;
-}
-
-// Make `bytes` of caller memory available on the device: returns the caller's pointer if it is
-// already device memory, else stages it through `b`.
-static int stage_in(cgnn_ctx* ctx, DevBuf& b, const void* src, size_t bytes, const void** out) {
-    if (!src) { *out = nullptr; return 0; }
-    if (is_device_ptr(src)) { *out = src; return 0; }
-    int rc = ensure(ctx, b, bytes);
-    if (rc) return rc;
-    CU(cudaMemcpyAsync(b.p, src, bytes, cudaMemcpyHostToDevice, ctx->stream));
-    *out = b.p;
-    return 0;
-}
-
-// Device-side landing buffer for an output: the caller's own pointer if it is device memory.
-static int stage_out(cgnn_ctx* ctx, DevBuf& b, void* dst, size_t bytes, void** out) {
-    if (!dst) { *out = nullptr; return 0; }
-    if (is_device_ptr(dst)) { *out = dst; return 0; }
-    int rc = ensure(ctx, b, bytes);
-    if (rc) return rc;
-    *out = b.p;
-    return 0;
-}
-
-static int copy_back(cgnn_ctx* ctx, void* dst, const void* dev, size_t bytes) {
-    if (!dst || dst == dev) return 0;
-    CU(cudaMemcpyAsync(dst, dev, bytes, cudaMemcpyDeviceToHost, ctx->stream));
-    return 0;
-}
-
-static int check_hp(cgnn_ctx* ctx, const cgnn_hparams* hp) {
-    if (!hp) return fail(ctx, CGNN_ERR_ARG, "hparams is NULL");
-    if (hp->h_layer_dim < 1 || hp->h_layer_dim > CGNN_MAX_H)
-        return fail(ctx, CGNN_ERR_LIMIT, "h_layer_dim=%d outside [1,%d]", hp->h_layer_dim, CGNN_MAX_H);
-    if (hp->train_epochs < 0 || hp->test_epochs < 0) return fail(ctx, CGNN_ERR_ARG, "negative epoch count");
-    if (hp->exp_policy < 0 || hp->exp_policy > 3) return fail(ctx, CGNN_ERR_ARG, "exp_policy=%d unknown", hp->exp_policy);
-    return 0;
 }
 
 template <int POL>
@@ -192,7 +102,8 @@ void cgnn_b200_destroy(cgnn_ctx* ctx) {
     if (!ctx) return;
     cudaSetDevice(ctx->device);
     DevBuf* bufs[] = {&ctx->xy, &ctx->nrows, &ctx->inst, &ctx->scores, &ctx->noise, &ctx->init, &ctx->trace,
-                      &ctx->pout, &ctx->counter, &ctx->dbg[0], &ctx->dbg[1], &ctx->dbg[2], &ctx->dbg[3], &ctx->dbg[4]};
+                      &ctx->pout, &ctx->counter, &ctx->dbg[0], &ctx->dbg[1], &ctx->dbg[2], &ctx->dbg[3], &ctx->dbg[4],
+                      &ctx->gT, &ctx->gdesc, &ctx->gtidx, &ctx->gsub, &ctx->gdata};
     for (DevBuf* b : bufs)
         if (b->p) cudaFree(b->p);
     if (ctx->ev0) cudaEventDestroy(ctx->ev0);

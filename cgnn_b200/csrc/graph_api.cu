@@ -1,0 +1,246 @@
+// C-ABI of the graph path: cgnn_b200_run_graph, cgnn_b200_graph_step_debug.  See include/cgnn_b200.h.
+#include <vector>
+
+#include "ctx.h"
+#include "graph.cuh"
+
+using namespace cgnn;
+
+// Gather rows (optionally a subset) of the row-major data matrix into the padded layout T[NP][DP].
+static __global__ void gather_rows_kernel(const float* __restrict__ data, int n_var, const int* __restrict__ subset,
+                                   int N, int NP, int DP, float* __restrict__ T) {
+    const size_t set = blockIdx.y;
+    const int* sub = subset ? subset + set * N : nullptr;
+    float* dst = T + set * size_t(NP) * DP;
+    for (int q = blockIdx.x * blockDim.x + threadIdx.x; q < NP * DP; q += gridDim.x * blockDim.x) {
+        const int r = q / DP, c = q - r * DP;
+        float v = 0.f;
+        if (r < N && c < n_var) v = data[size_t(sub ? sub[r] : r) * n_var + c];
+        dst[q] = v;
+    }
+}
+
+
+#define DECL(DP_) cudaError_t cgnn_launch_graph_dp##DP_(int, const GraphArgs&, int, size_t, cudaStream_t);
+DECL(8) DECL(16) DECL(20) DECL(24) DECL(32)
+#undef DECL
+
+static int pick_dp(int n_var) {
+    const int choices[5] = {8, 16, 20, 24, 32};
+    for (int c : choices)
+        if (n_var <= c) return c;
+    return 0;
+}
+
+static cudaError_t launch_graph(int dp, int pol, const GraphArgs& a, int grid, size_t smem, cudaStream_t st) {
+    switch (dp) {
+        case 8: return cgnn_launch_graph_dp8(pol, a, grid, smem, st);
+        case 16: return cgnn_launch_graph_dp16(pol, a, grid, smem, st);
+        case 20: return cgnn_launch_graph_dp20(pol, a, grid, smem, st);
+        case 24: return cgnn_launch_graph_dp24(pol, a, grid, smem, st);
+        case 32: return cgnn_launch_graph_dp32(pol, a, grid, smem, st);
+    }
+    return cudaErrorInvalidValue;
+}
+
+static int run_graph_impl(cgnn_ctx* ctx, const cgnn_hparams* hp, const float* data, int n_rows_total,
+                          const cgnn_graph_batch* gb, int n_runs, const int* row_subsets, int n_rows,
+                          unsigned long long uid_base, const float* noise, const float* init_params, int ld_params,
+                          float* scores, float* loss_trace, float* params_out, float* const dbg_host[5], int dbg_steps) {
+    if (!ctx) return CGNN_ERR_ARG;
+    ctx->err.clear();
+    int rc = check_hp(ctx, hp);
+    if (rc) return rc;
+    if (hp->h_layer_dim > CGNN_MAX_H_GRAPH)
+        return fail(ctx, CGNN_ERR_LIMIT, "graph path: h_layer_dim=%d exceeds CGNN_MAX_H_GRAPH=%d", hp->h_layer_dim, CGNN_MAX_H_GRAPH);
+    if (!data || !gb) return fail(ctx, CGNN_ERR_ARG, "data / graph batch is NULL");
+    if (!gb->node_col || !gb->n_parents || !gb->n_inputs || !gb->in_ptr || !gb->in_idx)
+        return fail(ctx, CGNN_ERR_ARG, "graph batch has a NULL array");
+    if (gb->n_graphs < 1 || n_runs < 1) return fail(ctx, CGNN_ERR_ARG, "n_graphs and n_runs must be >= 1");
+    const int n_var = gb->n_var, n_noise = gb->n_noise_cols;
+    if (n_var < 1 || n_var > CGNN_MAX_VARS) return fail(ctx, CGNN_ERR_LIMIT, "n_var=%d outside [1,%d]", n_var, CGNN_MAX_VARS);
+    if (n_noise < n_var) return fail(ctx, CGNN_ERR_ARG, "n_noise_cols=%d < n_var=%d (every node has its own noise column)", n_noise, n_var);
+    if (n_noise > 4096) return fail(ctx, CGNN_ERR_LIMIT, "too many noise columns");
+    if (n_rows < 1 || n_rows > CGNN_MAX_ROWS_GRAPH)
+        return fail(ctx, CGNN_ERR_LIMIT, "n_rows=%d outside [1,%d] (subsample first, CGNN.py:183-185)", n_rows, CGNN_MAX_ROWS_GRAPH);
+    if (row_subsets ? (n_rows > n_rows_total) : (n_rows != n_rows_total))
+        return fail(ctx, CGNN_ERR_ARG, "n_rows=%d inconsistent with n_rows_total=%d", n_rows, n_rows_total);
+    if (!scores && !dbg_host) return fail(ctx, CGNN_ERR_ARG, "scores is NULL");
+    CU(cudaSetDevice(ctx->device));
+
+    const int h = hp->h_layer_dim;
+    const int n_graphs = gb->n_graphs;
+    const int n_inst = dbg_host ? 1 : n_graphs * n_runs;
+    const int epochs = hp->train_epochs + hp->test_epochs;
+
+    // ---- descriptors ---------------------------------------------------------------------------
+    std::vector<GraphDesc> descs(n_graphs);
+    int p_max = 0;
+    for (int g = 0; g < n_graphs; ++g) {
+        GraphDesc& d = descs[g];
+        std::memset(&d, 0, sizeof d);
+        d.n_var = n_var; d.n_noise = n_noise;
+        const int base = gb->in_ptr[g], end = gb->in_ptr[g + 1];
+        if (end - base > GR_MAX_IN) return fail(ctx, CGNN_ERR_LIMIT, "graph %d has %d inputs in total (limit %d)", g, end - base, GR_MAX_IN);
+        int io = 0, po = 0;
+        unsigned int seen = 0;
+        for (int k = 0; k < n_var; ++k) {
+            const int col = gb->node_col[g * n_var + k], npar = gb->n_parents[g * n_var + k], nin = gb->n_inputs[g * n_var + k];
+            if (col < 0 || col >= n_var || (seen >> col & 1u)) return fail(ctx, CGNN_ERR_ARG, "graph %d: node_col is not a permutation", g);
+            if (npar < 0 || nin <= npar || base + io + nin > end) return fail(ctx, CGNN_ERR_ARG, "graph %d node %d: bad input counts", g, k);
+            for (int p = 0; p < nin; ++p) {
+                const int id = gb->in_idx[base + io + p];
+                if (p < npar) {
+                    if (id < 0 || id >= n_var || !(seen >> id & 1u))
+                        return fail(ctx, CGNN_ERR_ARG, "graph %d node %d: parent column %d is not generated yet (not a build order)", g, k, id);
+                } else if (id < 0 || id >= n_noise) {
+                    return fail(ctx, CGNN_ERR_ARG, "graph %d node %d: noise column %d out of range", g, k, id);
+                }
+                d.in_idx[io + p] = short(id);
+            }
+            seen |= 1u << col;
+            d.col[k] = short(col); d.n_par[k] = short(npar); d.n_in[k] = short(nin);
+            d.in_off[k] = io; d.par_off[k] = po;
+            io += nin;
+            po += nin * h + 2 * h + 1;
+        }
+        if (base + io != end) return fail(ctx, CGNN_ERR_ARG, "graph %d: in_ptr does not match the sum of n_inputs", g);
+        d.n_in_total = io; d.n_params = po;
+        p_max = std::max(p_max, po);
+    }
+    if ((init_params || params_out) && ld_params < p_max)
+        return fail(ctx, CGNN_ERR_ARG, "ld_params=%d smaller than the largest parameter count %d", ld_params, p_max);
+
+    const int DP = pick_dp(n_var);
+    const int NP = 32 * ((n_rows + 31) / 32);
+    GraphArgs a{};
+    const void* dp = nullptr;
+    void* op = nullptr;
+
+    // ---- observed matrix in the padded layout, one copy per row subset ------------------------------
+    if ((rc = stage_in(ctx, ctx->gdata, data, sizeof(float) * size_t(n_rows_total) * n_var, &dp))) return rc;
+    const float* d_data = static_cast<const float*>(dp);
+    const int n_T = row_subsets ? n_inst : 1;
+    const int* d_sub = nullptr;
+    if (row_subsets) {
+        if ((rc = stage_in(ctx, ctx->gsub, row_subsets, sizeof(int) * size_t(n_inst) * n_rows, &dp))) return rc;
+        d_sub = static_cast<const int*>(dp);
+    }
+    if ((rc = ensure(ctx, ctx->gT, sizeof(float) * size_t(n_T) * NP * DP))) return rc;
+    {
+        dim3 grid((NP * DP + 255) / 256, n_T);
+        gather_rows_kernel<<<grid, 256, 0, ctx->stream>>>(d_data, n_var, d_sub, n_rows, NP, DP, static_cast<float*>(ctx->gT.p));
+        CU(cudaGetLastError());
+    }
+    a.T = static_cast<const float*>(ctx->gT.p);
+    if (row_subsets) {
+        std::vector<int> ti(n_inst);
+        for (int k = 0; k < n_inst; ++k) ti[k] = k;
+        if ((rc = ensure(ctx, ctx->gtidx, sizeof(int) * n_inst))) return rc;
+        CU(cudaMemcpyAsync(ctx->gtidx.p, ti.data(), sizeof(int) * n_inst, cudaMemcpyHostToDevice, ctx->stream));
+        CU(cudaStreamSynchronize(ctx->stream));
+        a.t_index = static_cast<const int*>(ctx->gtidx.p);
+    }
+    if ((rc = ensure(ctx, ctx->gdesc, sizeof(GraphDesc) * n_graphs))) return rc;
+    CU(cudaMemcpyAsync(ctx->gdesc.p, descs.data(), sizeof(GraphDesc) * n_graphs, cudaMemcpyHostToDevice, ctx->stream));
+    a.desc = static_cast<const GraphDesc*>(ctx->gdesc.p);
+
+    // instance table: larger parameter count first
+    std::vector<int2> tab;
+    tab.reserve(size_t(n_graphs) * n_runs);
+    std::vector<int> order(n_graphs);
+    for (int g = 0; g < n_graphs; ++g) order[g] = g;
+    std::stable_sort(order.begin(), order.end(), [&](int x, int y) { return descs[x].n_params > descs[y].n_params; });
+    if (dbg_host) tab.push_back(make_int2(0, 0));
+    else
+        for (int g : order)
+            for (int r = 0; r < n_runs; ++r) tab.push_back(make_int2(g, g * n_runs + r));
+    if ((rc = ensure(ctx, ctx->inst, sizeof(int2) * n_inst))) return rc;
+    CU(cudaMemcpyAsync(ctx->inst.p, tab.data(), sizeof(int2) * n_inst, cudaMemcpyHostToDevice, ctx->stream));
+    a.inst = static_cast<const int2*>(ctx->inst.p);
+
+    if ((rc = stage_in(ctx, ctx->noise, noise, sizeof(float) * size_t(n_inst) * epochs * n_noise * n_rows, &dp))) return rc;
+    a.noise = static_cast<const float*>(dp);
+    if ((rc = stage_in(ctx, ctx->init, init_params, sizeof(float) * size_t(n_inst) * ld_params, &dp))) return rc;
+    a.init_params = static_cast<const float*>(dp);
+    if ((rc = stage_out(ctx, ctx->scores, scores, sizeof(float) * n_inst, &op))) return rc;
+    a.scores = static_cast<float*>(op);
+    if ((rc = stage_out(ctx, ctx->trace, loss_trace, sizeof(float) * size_t(n_inst) * epochs, &op))) return rc;
+    a.trace = static_cast<float*>(op);
+    if ((rc = stage_out(ctx, ctx->pout, params_out, sizeof(float) * size_t(n_inst) * ld_params, &op))) return rc;
+    a.params_out = static_cast<float*>(op);
+    if ((rc = ensure(ctx, ctx->counter, 256))) return rc;
+    a.counter = static_cast<int*>(ctx->counter.p);
+    CU(cudaMemsetAsync(a.counter, 0, 256, ctx->stream));
+
+    size_t dbg_bytes[5] = {0, 0, 0, 0, 0};
+    float* dbg_dev[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
+    if (dbg_host) {
+        const size_t P0 = size_t(descs[0].n_params);
+        dbg_bytes[0] = sizeof(float) * dbg_steps;
+        dbg_bytes[1] = dbg_bytes[2] = sizeof(float) * dbg_steps * size_t(n_rows) * n_var;
+        dbg_bytes[3] = dbg_bytes[4] = sizeof(float) * dbg_steps * P0;
+        for (int k = 0; k < 5; ++k) {
+            if ((rc = stage_out(ctx, ctx->dbg[k], dbg_host[k], dbg_bytes[k], &op))) return rc;
+            dbg_dev[k] = static_cast<float*>(op);
+        }
+        a.dbg_loss = dbg_dev[0]; a.dbg_pred = dbg_dev[1]; a.dbg_dldp = dbg_dev[2]; a.dbg_grad = dbg_dev[3]; a.dbg_params = dbg_dev[4];
+    }
+
+    a.n_inst = n_inst; a.N = n_rows; a.NP = NP; a.n_noise = n_noise; a.p_max = p_max;
+    a.h = h; a.train_epochs = hp->train_epochs; a.test_epochs = hp->test_epochs; a.trace_every = hp->trace_every;
+    a.lr = hp->learning_rate; a.init_std = hp->init_std; a.ld_params = ld_params;
+    a.key = make_uint2((unsigned int)(hp->seed & 0xffffffffu), (unsigned int)(hp->seed >> 32) ^ (unsigned int)(uid_base >> 32));
+    a.uid_base = (unsigned int)(uid_base & 0xffffffffu);
+
+    const size_t smem = gr_smem_bytes(NP, DP, n_noise, p_max);
+    if (smem > size_t(ctx->prop.sharedMemPerBlockOptin))
+        return fail(ctx, CGNN_ERR_LIMIT, "graph instance needs %zu B of shared memory (rows %d x cols %d, %d noise columns, %d parameters); "
+                    "device allows %zu", smem, n_rows, DP, n_noise, p_max, size_t(ctx->prop.sharedMemPerBlockOptin));
+    const int grid = std::min(n_inst, ctx->prop.multiProcessorCount);
+
+    CU(cudaEventRecord(ctx->ev0, ctx->stream));
+    cudaError_t le = launch_graph(DP, hp->exp_policy, a, grid, smem, ctx->stream);
+    if (le != cudaSuccess) return fail(ctx, CGNN_ERR_CUDA, "graph kernel launch: %s", cudaGetErrorString(le));
+    CU(cudaEventRecord(ctx->ev1, ctx->stream));
+    ctx->last_launches = 2;
+
+    if ((rc = copy_back(ctx, scores, a.scores, sizeof(float) * n_inst))) return rc;
+    if ((rc = copy_back(ctx, loss_trace, a.trace, sizeof(float) * size_t(n_inst) * epochs))) return rc;
+    if ((rc = copy_back(ctx, params_out, a.params_out, sizeof(float) * size_t(n_inst) * ld_params))) return rc;
+    if (dbg_host)
+        for (int k = 0; k < 5; ++k)
+            if ((rc = copy_back(ctx, dbg_host[k], dbg_dev[k], dbg_bytes[k]))) return rc;
+    CU(cudaStreamSynchronize(ctx->stream));
+    CU(cudaEventElapsedTime(&ctx->last_ms, ctx->ev0, ctx->ev1));
+    return CGNN_OK;
+}
+
+extern "C" {
+
+int cgnn_b200_run_graph(cgnn_ctx* ctx, const cgnn_hparams* hp, const float* data, int n_rows_total,
+                        const cgnn_graph_batch* graphs, int n_runs, const int* row_subsets, int n_rows,
+                        unsigned long long uid_base, const float* noise, const float* init_params, int ld_params,
+                        float* scores, float* loss_trace, float* params_out) {
+    return run_graph_impl(ctx, hp, data, n_rows_total, graphs, n_runs, row_subsets, n_rows, uid_base, noise, init_params,
+                          ld_params, scores, loss_trace, params_out, nullptr, 0);
+}
+
+int cgnn_b200_graph_step_debug(cgnn_ctx* ctx, const cgnn_hparams* hp, const float* data, int n_rows,
+                               const cgnn_graph_batch* graph, int n_steps, const float* noise, const float* init_params,
+                               int n_params, float* out_loss, float* out_pred, float* out_dldp, float* out_grad,
+                               float* out_params) {
+    if (!ctx) return CGNN_ERR_ARG;
+    if (!hp) return fail(ctx, CGNN_ERR_ARG, "hparams is NULL");
+    if (!noise || !init_params) return fail(ctx, CGNN_ERR_ARG, "step_debug needs caller-supplied noise and parameters");
+    if (n_steps < 1) return fail(ctx, CGNN_ERR_ARG, "n_steps must be >= 1");
+    cgnn_hparams h2 = *hp;
+    h2.train_epochs = n_steps;
+    h2.test_epochs = 0;
+    h2.trace_every = 0;
+    float* dbg[5] = {out_loss, out_pred, out_dldp, out_grad, out_params};
+    return run_graph_impl(ctx, &h2, data, n_rows, graph, 1, nullptr, n_rows, 0ULL, noise, init_params, n_params, nullptr,
+                          nullptr, nullptr, dbg, n_steps);
+}
+
+}  // extern "C"

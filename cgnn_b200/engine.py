@@ -150,3 +150,67 @@ class Engine:
                                                      _ptr(out["dldy"]), _ptr(out["grad"]), _ptr(out["params"]))
         self._check(rc, "cgnn_b200_pairwise_step_debug")
         return out
+
+    # -- graph ------------------------------------------------------------------------------
+    def run_graph(self, data, plans, n_runs=None, row_subsets=None, uid_base=0, noise=None, init_params=None,
+                  want_trace=False, want_params=False, **kw):
+        """Score every (candidate graph, run) instance.
+
+        data: [n_rows_total, n_var] float32 (numpy or torch), columns as the plans' `col` indices.
+        plans: list of plans (cgnn_b200.plan.build_plan).  row_subsets: None or int32
+        [n_graphs*n_runs, n_rows] (the per-call subsample of CGNN.py:183-185).
+        Returns dict(scores [n_graphs, n_runs], trace?, params?).
+        """
+        from .plan import GraphBatch, n_params
+        hp = make_hparams(**kw)
+        n_runs = int(n_runs if n_runs is not None else kw.get("nb_runs", SETTINGS.NB_RUNS))
+        if isinstance(data, np.ndarray):
+            data = np.ascontiguousarray(data, dtype=np.float32)
+        n_total = int(data.shape[0])
+        gb = GraphBatch(plans)
+        n_graphs = len(plans)
+        n_inst = n_graphs * n_runs
+        if row_subsets is not None:
+            row_subsets = np.ascontiguousarray(row_subsets, np.int32).reshape(n_inst, -1)
+            n_rows = row_subsets.shape[1]
+        else:
+            n_rows = n_total
+        ld = max(n_params(p, hp.h_layer_dim) for p in plans)
+        epochs = hp.train_epochs + hp.test_epochs
+        if noise is not None:
+            noise = np.ascontiguousarray(noise, np.float32)
+            if noise.size != n_inst * epochs * gb.struct.n_noise_cols * n_rows:
+                raise ValueError("noise must be [n_inst, epochs, n_noise_cols, n_rows]")
+        if init_params is not None:
+            init_params = np.ascontiguousarray(init_params, np.float32)
+            if init_params.size != n_inst * ld:
+                raise ValueError("init_params must be [n_inst, %d]" % ld)
+        scores = np.empty((n_graphs, n_runs), np.float32)
+        trace = np.empty((n_inst, epochs), np.float32) if want_trace else None
+        pout = np.empty((n_inst, ld), np.float32) if want_params else None
+        rc = self._lib.cgnn_b200_run_graph(self._h, C.byref(hp), _ptr(data), n_total, C.byref(gb.struct), n_runs,
+                                           _ptr(row_subsets), n_rows, C.c_ulonglong(int(uid_base)), _ptr(noise),
+                                           _ptr(init_params), ld, _ptr(scores), _ptr(trace), _ptr(pout))
+        self._check(rc, "cgnn_b200_run_graph")
+        return dict(scores=scores, trace=trace, params=pout)
+
+    def graph_step_debug(self, data, plan, noise, init_params, **kw):
+        """Parity probe: consecutive train steps of ONE graph instance."""
+        from .plan import GraphBatch, n_params
+        hp = make_hparams(**kw)
+        data = np.ascontiguousarray(data, np.float32)
+        noise = np.ascontiguousarray(noise, np.float32)
+        init_params = np.ascontiguousarray(init_params, np.float32)
+        gb = GraphBatch([plan])
+        n_rows, n_var = data.shape
+        n_steps = noise.shape[0]
+        P = n_params(plan, hp.h_layer_dim)
+        assert noise.shape == (n_steps, plan["n_noise"], n_rows) and init_params.shape == (P,)
+        out = dict(loss=np.empty(n_steps, np.float32), pred=np.empty((n_steps, n_rows, n_var), np.float32),
+                   dldp=np.empty((n_steps, n_rows, n_var), np.float32), grad=np.empty((n_steps, P), np.float32),
+                   params=np.empty((n_steps, P), np.float32))
+        rc = self._lib.cgnn_b200_graph_step_debug(self._h, C.byref(hp), _ptr(data), n_rows, C.byref(gb.struct), n_steps,
+                                                  _ptr(noise), _ptr(init_params), P, _ptr(out["loss"]), _ptr(out["pred"]),
+                                                  _ptr(out["dldp"]), _ptr(out["grad"]), _ptr(out["params"]))
+        self._check(rc, "cgnn_b200_graph_step_debug")
+        return out

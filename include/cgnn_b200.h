@@ -30,6 +30,9 @@ extern "C" {
 #define CGNN_N_GAMMAS          7        /* Loss.py:10 - fixed at compile time, like the reference */
 #define CGNN_MAX_ROWS_PAIRWISE 2048     /* reference subsamples to SETTINGS.max_nb_points = 1500 (GNN.py:150-153) */
 #define CGNN_MAX_H             64       /* hidden width limit (reference default 20, scripts use 30) */
+#define CGNN_MAX_H_GRAPH       32       /* hidden width limit of the graph path (reference default 20) */
+#define CGNN_MAX_VARS          32       /* variables (columns) per graph */
+#define CGNN_MAX_ROWS_GRAPH    1536     /* rows per graph instance after subsampling (SETTINGS.max_nb_points = 1500) */
 
 typedef enum cgnn_status {
     CGNN_OK            =  0,
@@ -50,8 +53,10 @@ typedef struct cgnn_hparams {
     int   test_epochs;        /* SETTINGS.test_epochs  (Settings.py:38) */
     float learning_rate;      /* SETTINGS.learning_rate (Settings.py:31) */
     float init_std;           /* SETTINGS.init_weights  (Settings.py:32) */
-    int   exp_policy;         /* how the 7 Gaussian kernels of one pair evaluation are produced:
-                                 0 = seven MUFU ex2;  1 = five MUFU ex2, gamma 0.5 and 1 by squaring gamma 0.25 */
+    int   exp_policy;         /* how the 7 Gaussian kernels of one pair evaluation are produced (all within the
+                                 1e-5 parity bound, measured 2e-6): 0 = seven MUFU ex2; 1 = five (gamma 0.5, 1 by
+                                 squaring gamma 0.25); 2 = four (+ gamma 0.05 = 10th power of 0.005);
+                                 3 = three (+ gamma 5 = 5th power of gamma 1) */
     int   trace_every;        /* >0: also compute the (pre-update) training loss on every trace_every-th
                                  train step into loss_trace (GNN.py:98-102 prints every 100th); 0 = never */
     int   reserved0;
@@ -119,6 +124,64 @@ int  cgnn_b200_pairwise_step_debug(cgnn_ctx* ctx, const cgnn_hparams* hp,
                                    const float* noise, const float* init_params,
                                    float* out_loss, float* out_yhat, float* out_dldy,
                                    float* out_grad, float* out_params);
+
+/* ---- graph CGNN and CGNN with hidden variables --------------------------------------------- */
+
+/* A batch of candidate graphs over the same n_var variables, each given as its nodes in the
+ * reference's BUILD ORDER (repeated scan of graph.get_list_nodes(), a node is emitted once all its
+ * parents are, Code/cgnn/CGNN.py:63-69).  Node k of graph g
+ *   writes data column          node_col[g*n_var + k]
+ *   has n_parents[g*n_var + k]  generated parent columns (graph.get_parents order, CGNN.py:67,76)
+ *   has n_inputs[g*n_var + k]   inputs in total = parents, then its own noise column, then - hidden-variable
+ *                               model only - one shared noise column per skeleton neighbour
+ *                               (graph.skeleton.get_neighbors order, CGNN_confounders.py:82-96)
+ * in_idx holds, graph after graph (graph g occupies [in_ptr[g], in_ptr[g+1])) and node after node, the
+ * parent COLUMN indices followed by the NOISE-COLUMN ids.  Noise column ids: c < n_var is the own noise
+ * of the node writing column c; n_var + e is the noise shared over skeleton edge e
+ * (skeleton.get_list_edges_without_duplicate order, CGNN_confounders.py:64-72).
+ * Parameters of a graph, flat: per node in build order [W_in (n_inputs x h) | b_in (h) | W_out (h) | b_out]. */
+typedef struct cgnn_graph_batch {
+    int n_graphs;
+    int n_var;
+    int n_noise_cols;         /* n_var for CGNN; n_var + number of skeleton edges for the hidden-variable model */
+    const int* node_col;      /* [n_graphs][n_var]  (host memory) */
+    const int* n_parents;     /* [n_graphs][n_var] */
+    const int* n_inputs;      /* [n_graphs][n_var] */
+    const int* in_ptr;        /* [n_graphs + 1] */
+    const int* in_idx;        /* [in_ptr[n_graphs]] */
+} cgnn_graph_batch;
+
+/* Scores every (candidate graph, run) instance: mean test MMD after training (no complexity penalty,
+ * no finite-filter: CGNN.py:217 and CGNN_confounders.py:236-237 stay with the caller).
+ * Replaces run_CGNN_tf + CGNN_tf.{__init__,train,evaluate} (Code/cgnn/CGNN.py:35-195) and
+ * run_CGNN_confounders_tf + CGNN_confounders_tf.* (Code/cgnn/CGNN_confounders.py:37-216) for all runs of
+ * all candidates at once - the unit a hill-climbing sweep evaluates (CGNN.py:214-215,237-238).
+ *
+ *   data          [n_rows_total][n_var] fp32 row-major, columns in the order node_col refers to
+ *   row_subsets   NULL (n_rows == n_rows_total, every instance sees all rows) or [n_inst][n_rows] row indices:
+ *                 the per-call random subsample of CGNN.py:183-185, drawn by the caller
+ *   noise         NULL (in-kernel Philox) or [n_inst][train+test epochs][n_noise_cols][n_rows]
+ *   init_params   NULL (in-kernel N(0, init_std^2)) or [n_inst][ld_params]
+ *   scores        out [n_graphs][n_runs]
+ *   loss_trace    NULL or out [n_inst][train+test epochs];  params_out  NULL or out [n_inst][ld_params]
+ * with n_inst = n_graphs*n_runs, instance index g*n_runs + r, Philox stream uid_base + that index. */
+int  cgnn_b200_run_graph(cgnn_ctx* ctx, const cgnn_hparams* hp,
+                         const float* data, int n_rows_total,
+                         const cgnn_graph_batch* graphs, int n_runs,
+                         const int* row_subsets, int n_rows,
+                         unsigned long long uid_base,
+                         const float* noise, const float* init_params, int ld_params,
+                         float* scores, float* loss_trace, float* params_out);
+
+/* Parity probe for the graph path: n_steps consecutive train steps of graph 0 of the batch with
+ * caller-supplied noise [n_steps][n_noise_cols][n_rows] and parameters [n_params]; dumps per step the
+ * pre-update loss, the generated matrix [n_rows][n_var], dLoss/dPred [n_rows][n_var], the parameter
+ * gradient and the parameters after Adam (one sess.run of CGNN.py:118-121).  Host buffers. */
+int  cgnn_b200_graph_step_debug(cgnn_ctx* ctx, const cgnn_hparams* hp,
+                                const float* data, int n_rows, const cgnn_graph_batch* graph, int n_steps,
+                                const float* noise, const float* init_params, int n_params,
+                                float* out_loss, float* out_pred, float* out_dldp,
+                                float* out_grad, float* out_params);
 
 /* ---- pairwise GNN for callers that must not allocate device memory ------------------------ */
 

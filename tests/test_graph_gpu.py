@@ -1,0 +1,158 @@
+"""Parity of the CUDA graph path (CGNN and the hidden-variable variant) with the fp64 oracle,
+through the C ABI.  Tolerance as in test_pairwise_gpu.py (north_star: 1e-5 relative)."""
+import numpy as np
+import pytest
+
+from util import relerr
+
+pytestmark = pytest.mark.gpu
+TOL = 1e-5
+
+
+def random_dag(n_var, max_par, seed, with_skeleton=False):
+    """A DirectedGraph over V0..V{n-1} (random order of edge insertion) and matching data columns."""
+    from cgnn_b200.utils.Graph import DirectedGraph, UndirectedGraph
+    import pandas as pd
+    rng = np.random.default_rng(seed)
+    perm = rng.permutation(n_var)
+    edges = []
+    for k in range(1, n_var):
+        for p in rng.choice(k, size=min(k, int(rng.integers(1, max_par + 1))), replace=False):
+            edges.append(("V%d" % perm[p], "V%d" % perm[k]))
+    order = rng.permutation(len(edges))
+    skel = None
+    if with_skeleton:
+        extra = [("V%d" % perm[0], "V%d" % perm[n_var - 1])] if n_var > 3 else []
+        skel = UndirectedGraph(pd.DataFrame([edges[o] for o in order] + extra, columns=["Cause", "Effect"]))
+    g = DirectedGraph(skeleton=skel) if with_skeleton else DirectedGraph()
+    for o in order:
+        g.add(edges[o][0], edges[o][1], float(rng.uniform(0.1, 1)))
+    return g
+
+
+def make_data(n, n_var, seed):
+    rng = np.random.default_rng(seed)
+    z = rng.normal(size=(n, n_var))
+    mix = rng.normal(size=(n_var, n_var)) * 0.5 + np.eye(n_var)
+    d = np.tanh(z @ mix) + 0.1 * z
+    if n == 1:
+        return d.astype(np.float32)
+    return ((d - d.mean(0)) / d.std(0)).astype(np.float32)
+
+
+def _oracle_steps(data, plan, noise, theta0, h):
+    from oracle import cgnn as oc
+    from oracle.adam import TFAdam
+    theta = theta0.astype(np.float64)
+    opt = TFAdam(theta.size, 0.01)
+    out = dict(loss=[], pred=[], dldp=[], grad=[], params=[])
+    for it in range(noise.shape[0]):
+        r = oc.step_debug(theta, data.astype(np.float64), noise[it].astype(np.float64), plan, h)
+        theta = opt.step(theta, r["grad"])
+        out["loss"].append(r["loss"]); out["pred"].append(r["pred"]); out["dldp"].append(r["dloss_dpred"])
+        out["grad"].append(r["grad"]); out["params"].append(theta.copy())
+    return {k: np.array(v) for k, v in out.items()}
+
+
+@pytest.mark.parametrize("pol", [0, 3])
+@pytest.mark.parametrize("n,n_var,h,conf", [(100, 5, 8, False), (257, 11, 20, False), (64, 22, 20, False),
+                                            (33, 3, 32, False), (96, 8, 12, True), (130, 19, 20, True), (1, 2, 4, False)])
+def test_graph_step_debug_matches_oracle(engine, n, n_var, h, conf, pol):
+    from cgnn_b200.plan import build_plan, n_params
+    from oracle import cgnn as oc
+    g = random_dag(n_var, 3, 7 * n_var + n, with_skeleton=conf)
+    plan = build_plan(g, confounders=conf)
+    oplan = oc.build_plan(g, confounders=conf)
+    assert [(a["col"], a["parents"], a["noise"]) for a in plan["nodes"]] == \
+           [(b["col"], b["parents"], b["noise"]) for b in oplan["nodes"]]
+    data = make_data(n, n_var, n)
+    rng = np.random.default_rng(n + n_var)
+    P = n_params(plan, h)
+    assert P == oc.n_params(oplan, h)
+    theta0 = (0.05 * rng.normal(size=P)).astype(np.float32)
+    steps = 3
+    noise = rng.normal(size=(steps, plan["n_noise"], n)).astype(np.float32)
+    got = engine.graph_step_debug(data, plan, noise, theta0, h_layer_dim=h, exp_policy=pol)
+    ref = _oracle_steps(data, oplan, noise, theta0, h)
+    for s in range(steps):
+        assert abs(got["loss"][s] - ref["loss"][s]) <= TOL * abs(ref["loss"][s]), (s, got["loss"][s], ref["loss"][s])
+        assert relerr(got["pred"][s], ref["pred"][s]) < TOL
+        assert relerr(got["dldp"][s], ref["dldp"][s]) < TOL
+        assert relerr(got["grad"][s], ref["grad"][s]) < TOL
+        assert relerr(got["params"][s], ref["params"][s]) < TOL
+
+
+def test_graph_full_size_step(engine):
+    """The shapes of the bundled graph example: 500 rows, 22 variables, h = 20."""
+    from cgnn_b200.plan import build_plan, n_params
+    from oracle import cgnn as oc
+    n, n_var, h = 500, 22, 20
+    g = random_dag(n_var, 2, 5)
+    plan = build_plan(g)
+    data = make_data(n, n_var, 3)
+    rng = np.random.default_rng(1)
+    theta0 = (0.05 * rng.normal(size=n_params(plan, h))).astype(np.float32)
+    noise = rng.normal(size=(2, plan["n_noise"], n)).astype(np.float32)
+    got = engine.graph_step_debug(data, plan, noise, theta0, h_layer_dim=h, exp_policy=3)
+    ref = _oracle_steps(data, oc.build_plan(g), noise, theta0, h)
+    for s in range(2):
+        assert abs(got["loss"][s] - ref["loss"][s]) <= TOL * abs(ref["loss"][s])
+        assert relerr(got["dldp"][s], ref["dldp"][s]) < TOL
+        assert relerr(got["grad"][s], ref["grad"][s]) < TOL
+
+
+def test_run_graph_external_noise_matches_oracle(engine):
+    from cgnn_b200.plan import build_plan, n_params
+    from oracle import cgnn as oc
+    n, n_var, h, tr, te, runs = 90, 6, 10, 20, 5, 2
+    graphs = [random_dag(n_var, 2, 40 + k) for k in range(3)]
+    plans = [build_plan(g, columns=["V%d" % c for c in range(n_var)]) for g in graphs]
+    data = make_data(n, n_var, 9)
+    rng = np.random.default_rng(4)
+    ld = max(n_params(p, h) for p in plans)
+    n_inst = len(plans) * runs
+    init = (0.05 * rng.normal(size=(n_inst, ld))).astype(np.float32)
+    noise = rng.normal(size=(n_inst, tr + te, n_var, n)).astype(np.float32)
+    r = engine.run_graph(data, plans, n_runs=runs, noise=noise, init_params=init, want_trace=True, want_params=True,
+                         h_layer_dim=h, train_epochs=tr, test_epochs=te, trace_every=1, exp_policy=0)
+    for gi, plan in enumerate(plans):
+        P = n_params(plan, h)
+        for run in range(runs):
+            k = gi * runs + run
+            theta, losses, _ = oc.train(init[k, :P], data.astype(np.float64), noise[k, :tr].astype(np.float64), plan, h)
+            score, ev = oc.evaluate(theta, data.astype(np.float64), noise[k, tr:].astype(np.float64), plan, h)
+            assert relerr(r["trace"][k, :tr], losses) < 2e-5
+            assert relerr(r["trace"][k, tr:], ev) < 2e-5
+            assert relerr(r["params"][k, :P], theta) < 1e-4
+            assert abs(r["scores"][gi, run] - score) < 2e-5 * abs(score)
+
+
+def test_run_graph_determinism_subsets_and_limits(engine):
+    from cgnn_b200 import EngineError
+    from cgnn_b200.plan import build_plan
+    n_var = 7
+    g = random_dag(n_var, 2, 3)
+    cols = ["V%d" % c for c in range(n_var)]
+    plans = [build_plan(g, columns=cols)] * 2
+    data = make_data(300, n_var, 2)
+    kw = dict(n_runs=3, h_layer_dim=10, train_epochs=15, test_epochs=4, seed=77)
+    a = engine.run_graph(data, plans, **kw)["scores"].copy()
+    b = engine.run_graph(data, plans, **kw)["scores"].copy()
+    assert np.array_equal(a, b) and np.all(np.isfinite(a)) and np.all(a > 0)
+    assert not np.array_equal(a[0], a[1])            # same graph, different Philox streams
+    # the second graph alone with the matching uid_base reproduces its rows
+    c = engine.run_graph(data, plans[1:], uid_base=3, **kw)["scores"]
+    assert np.array_equal(a[1:], c)
+    # row subsets (CGNN.py:183-185): identity subset == no subset
+    ident = np.tile(np.arange(300, dtype=np.int32), (6, 1))
+    d = engine.run_graph(data, plans, row_subsets=ident, **kw)["scores"]
+    assert np.array_equal(a, d)
+    sub = np.stack([np.random.default_rng(k).permutation(300)[:200] for k in range(6)]).astype(np.int32)
+    e = engine.run_graph(data, plans, row_subsets=sub, **kw)["scores"]
+    one = engine.run_graph(np.ascontiguousarray(data[sub[4]]), plans[1:], n_runs=1, uid_base=4,
+                           **{k: v for k, v in kw.items() if k != "n_runs"})["scores"]
+    assert np.array_equal(e[1, 1], one[0, 0])
+    with pytest.raises(EngineError):
+        engine.run_graph(data, plans, n_runs=1, h_layer_dim=33)
+    with pytest.raises(EngineError):
+        engine.run_graph(np.zeros((1600, n_var), np.float32), plans, n_runs=1)
