@@ -38,7 +38,7 @@ SYMBOLS = {
     "cgnn_b200_pairwise_step_debug": (C.c_int, [_V, C.POINTER(Hparams), _V, C.c_int, C.c_int, _V, _V,
                                                 _V, _V, _V, _V, _V]),
     "cgnn_b200_run_graph": (C.c_int, [_V, C.POINTER(Hparams), _V, C.c_int, C.POINTER(GraphBatchStruct), C.c_int, _V, C.c_int,
-                                      C.c_ulonglong, _V, _V, C.c_int, _V, _V, _V]),
+                                      C.c_ulonglong, _V, _V, _V, C.c_int, _V, _V, _V]),
     "cgnn_b200_graph_step_debug": (C.c_int, [_V, C.POINTER(Hparams), _V, C.c_int, C.POINTER(GraphBatchStruct), C.c_int, _V, _V,
                                              C.c_int, _V, _V, _V, _V, _V]),
     "cgnn_b200_probe_peak": (C.c_int, [_V, C.c_int, C.c_int, C.POINTER(C.c_double)]),

@@ -103,7 +103,7 @@ void cgnn_b200_destroy(cgnn_ctx* ctx) {
     cudaSetDevice(ctx->device);
     DevBuf* bufs[] = {&ctx->xy, &ctx->nrows, &ctx->inst, &ctx->scores, &ctx->noise, &ctx->init, &ctx->trace,
                       &ctx->pout, &ctx->counter, &ctx->dbg[0], &ctx->dbg[1], &ctx->dbg[2], &ctx->dbg[3], &ctx->dbg[4],
-                      &ctx->gT, &ctx->gdesc, &ctx->gtidx, &ctx->gsub, &ctx->gdata};
+                      &ctx->gT, &ctx->gdesc, &ctx->gtidx, &ctx->gsub, &ctx->gdata, &ctx->guid};
     for (DevBuf* b : bufs)
         if (b->p) cudaFree(b->p);
     if (ctx->ev0) cudaEventDestroy(ctx->ev0);

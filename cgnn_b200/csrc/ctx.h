@@ -27,7 +27,7 @@ struct cgnn_ctx {
     int pw_ctas_per_sm = 0;
     // staging buffers (grow-only)
     DevBuf xy, nrows, inst, scores, noise, init, trace, pout, counter, dbg[5];
-    DevBuf gT, gdesc, gtidx, gsub, gdata;      // graph path
+    DevBuf gT, gdesc, gtidx, gsub, gdata, guid;      // graph path
 };
 
 static inline int fail(cgnn_ctx* c, int code, const char* fmt, ...) {

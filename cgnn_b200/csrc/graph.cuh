@@ -44,11 +44,11 @@ struct GraphArgs {
     const int* t_index;        // NULL (all instances use T[0]) or [n_inst] by out index
     const GraphDesc* desc;     // [n_graphs]
     const int2* inst;          // [n_inst] (graph, out index)
+    const unsigned long long* inst_uid;   // [n_inst] Philox stream id of each queue entry
     int n_inst, N, NP, n_noise, p_max;
     int h, train_epochs, test_epochs, trace_every;
     float lr, init_std;
     uint2 key;
-    unsigned int uid_base;
     const float* noise;        // NULL or [n_inst][epochs][n_noise][N]
     const float* init_params;  // NULL or [n_inst][ld_params]
     int ld_params;
@@ -79,13 +79,13 @@ __host__ __device__ inline size_t gr_smem_bytes(int NP, int DP, int n_noise, int
 
 // ---- noise of one row block into the warp's buffer -------------------------------------------
 __device__ __forceinline__ void gr_fill_noise(const GrSmem& s, const GraphArgs& a, float* nb, int i, int lane, int step,
-                                              unsigned int uid, const float* noise_step) {
+                                              unsigned int uid, uint2 key, const float* noise_step) {
     const int nn = s.desc->n_noise;
     if (noise_step) {
         for (int c = 0; c < nn; ++c) nb[c * 32 + lane] = (i < a.N) ? noise_step[size_t(c) * a.N + i] : 0.f;
     } else {
         for (int q = 0; 4 * q < nn; ++q) {
-            const float4 n = normal4(philox4x32_10(make_uint4(i, step, GR_STREAM_NOISE0 + q, uid), a.key));
+            const float4 n = normal4(philox4x32_10(make_uint4(i, step, GR_STREAM_NOISE0 + q, uid), key));
             nb[(4 * q + 0) * 32 + lane] = n.x; nb[(4 * q + 1) * 32 + lane] = n.y;
             nb[(4 * q + 2) * 32 + lane] = n.z; nb[(4 * q + 3) * 32 + lane] = n.w;
         }
@@ -294,7 +294,9 @@ __global__ void __launch_bounds__(GR_NT, 1) graph_kernel(const GraphArgs a) {
         if (s_inst >= a.n_inst) break;
         const int2 inst = a.inst[s_inst];
         const int out = inst.y;
-        const unsigned int uid = a.uid_base + (unsigned int)out;
+        const unsigned long long uid64 = a.inst_uid[s_inst];
+        const unsigned int uid = (unsigned int)(uid64 & 0xffffffffull);
+        const uint2 key = make_uint2(a.key.x, a.key.y ^ (unsigned int)(uid64 >> 32));
         const float* T = a.T + size_t(a.t_index ? a.t_index[out] : 0) * a.NP * DP;
         const float* noise = a.noise ? a.noise + size_t(out) * epochs * a.n_noise * N : nullptr;
 
@@ -312,7 +314,7 @@ __global__ void __launch_bounds__(GR_NT, 1) graph_kernel(const GraphArgs a) {
             if (q < P) {
                 if (a.init_params) th = a.init_params[size_t(out) * a.ld_params + q];
                 else {
-                    const float4 n = normal4(philox4x32_10(make_uint4(q >> 2, 0u, STREAM_INIT, uid), a.key));
+                    const float4 n = normal4(philox4x32_10(make_uint4(q >> 2, 0u, STREAM_INIT, uid), key));
                     const int e = q & 3;
                     th = a.init_std * (e == 0 ? n.x : e == 1 ? n.y : e == 2 ? n.z : n.w);
                 }
@@ -347,7 +349,7 @@ __global__ void __launch_bounds__(GR_NT, 1) graph_kernel(const GraphArgs a) {
             // ---- generator forward, all rows ------------------------------------------------
             for (int rb = warp; rb < NB; rb += GR_NW) {
                 const int i = 32 * rb + lane;
-                gr_fill_noise(s, a, nb, i, lane, it, uid, noise_step);
+                gr_fill_noise(s, a, nb, i, lane, it, uid, key, noise_step);
                 gr_forward_block<DP>(s, nb, i, lane, h);
                 __syncwarp();
             }
@@ -392,7 +394,7 @@ __global__ void __launch_bounds__(GR_NT, 1) graph_kernel(const GraphArgs a) {
                 }
                 if (a.dbg_dldp && i < N)
                     for (int c = 0; c < s.desc->n_var; ++c) a.dbg_dldp[(size_t(it) * N + i) * s.desc->n_var + c] = gl[c];
-                gr_fill_noise(s, a, nb, i, lane, it, uid, noise_step);
+                gr_fill_noise(s, a, nb, i, lane, it, uid, key, noise_step);
                 gr_backward_block<DP>(s, nb, i, lane, h, gl);
                 __syncwarp();
             }

@@ -45,7 +45,7 @@ static cudaError_t launch_graph(int dp, int pol, const GraphArgs& a, int grid, s
 
 static int run_graph_impl(cgnn_ctx* ctx, const cgnn_hparams* hp, const float* data, int n_rows_total,
                           const cgnn_graph_batch* gb, int n_runs, const int* row_subsets, int n_rows,
-                          unsigned long long uid_base, const float* noise, const float* init_params, int ld_params,
+                          unsigned long long uid_base, const unsigned long long* graph_uids, const float* noise, const float* init_params, int ld_params,
                           float* scores, float* loss_trace, float* params_out, float* const dbg_host[5], int dbg_steps) {
     if (!ctx) return CGNN_ERR_ARG;
     ctx->err.clear();
@@ -151,13 +151,21 @@ static int run_graph_impl(cgnn_ctx* ctx, const cgnn_hparams* hp, const float* da
     std::vector<int> order(n_graphs);
     for (int g = 0; g < n_graphs; ++g) order[g] = g;
     std::stable_sort(order.begin(), order.end(), [&](int x, int y) { return descs[x].n_params > descs[y].n_params; });
-    if (dbg_host) tab.push_back(make_int2(0, 0));
+    std::vector<unsigned long long> uids;
+    uids.reserve(size_t(n_graphs) * n_runs);
+    if (dbg_host) { tab.push_back(make_int2(0, 0)); uids.push_back(uid_base); }
     else
         for (int g : order)
-            for (int r = 0; r < n_runs; ++r) tab.push_back(make_int2(g, g * n_runs + r));
+            for (int r = 0; r < n_runs; ++r) {
+                tab.push_back(make_int2(g, g * n_runs + r));
+                uids.push_back(graph_uids ? graph_uids[g] + (unsigned long long)r : uid_base + (unsigned long long)(g * n_runs + r));
+            }
     if ((rc = ensure(ctx, ctx->inst, sizeof(int2) * n_inst))) return rc;
     CU(cudaMemcpyAsync(ctx->inst.p, tab.data(), sizeof(int2) * n_inst, cudaMemcpyHostToDevice, ctx->stream));
     a.inst = static_cast<const int2*>(ctx->inst.p);
+    if ((rc = ensure(ctx, ctx->guid, sizeof(unsigned long long) * n_inst))) return rc;
+    CU(cudaMemcpyAsync(ctx->guid.p, uids.data(), sizeof(unsigned long long) * n_inst, cudaMemcpyHostToDevice, ctx->stream));
+    a.inst_uid = static_cast<const unsigned long long*>(ctx->guid.p);
 
     if ((rc = stage_in(ctx, ctx->noise, noise, sizeof(float) * size_t(n_inst) * epochs * n_noise * n_rows, &dp))) return rc;
     a.noise = static_cast<const float*>(dp);
@@ -190,8 +198,7 @@ static int run_graph_impl(cgnn_ctx* ctx, const cgnn_hparams* hp, const float* da
     a.n_inst = n_inst; a.N = n_rows; a.NP = NP; a.n_noise = n_noise; a.p_max = p_max;
     a.h = h; a.train_epochs = hp->train_epochs; a.test_epochs = hp->test_epochs; a.trace_every = hp->trace_every;
     a.lr = hp->learning_rate; a.init_std = hp->init_std; a.ld_params = ld_params;
-    a.key = make_uint2((unsigned int)(hp->seed & 0xffffffffu), (unsigned int)(hp->seed >> 32) ^ (unsigned int)(uid_base >> 32));
-    a.uid_base = (unsigned int)(uid_base & 0xffffffffu);
+    a.key = make_uint2((unsigned int)(hp->seed & 0xffffffffu), (unsigned int)(hp->seed >> 32));
 
     const size_t smem = gr_smem_bytes(NP, DP, n_noise, p_max);
     if (smem > size_t(ctx->prop.sharedMemPerBlockOptin))
@@ -220,9 +227,9 @@ extern "C" {
 
 int cgnn_b200_run_graph(cgnn_ctx* ctx, const cgnn_hparams* hp, const float* data, int n_rows_total,
                         const cgnn_graph_batch* graphs, int n_runs, const int* row_subsets, int n_rows,
-                        unsigned long long uid_base, const float* noise, const float* init_params, int ld_params,
-                        float* scores, float* loss_trace, float* params_out) {
-    return run_graph_impl(ctx, hp, data, n_rows_total, graphs, n_runs, row_subsets, n_rows, uid_base, noise, init_params,
+                        unsigned long long uid_base, const unsigned long long* graph_uids, const float* noise,
+                        const float* init_params, int ld_params, float* scores, float* loss_trace, float* params_out) {
+    return run_graph_impl(ctx, hp, data, n_rows_total, graphs, n_runs, row_subsets, n_rows, uid_base, graph_uids, noise, init_params,
                           ld_params, scores, loss_trace, params_out, nullptr, 0);
 }
 
@@ -239,7 +246,7 @@ int cgnn_b200_graph_step_debug(cgnn_ctx* ctx, const cgnn_hparams* hp, const floa
     h2.test_epochs = 0;
     h2.trace_every = 0;
     float* dbg[5] = {out_loss, out_pred, out_dldp, out_grad, out_params};
-    return run_graph_impl(ctx, &h2, data, n_rows, graph, 1, nullptr, n_rows, 0ULL, noise, init_params, n_params, nullptr,
+    return run_graph_impl(ctx, &h2, data, n_rows, graph, 1, nullptr, n_rows, 0ULL, nullptr, noise, init_params, n_params, nullptr,
                           nullptr, nullptr, dbg, n_steps);
 }
 

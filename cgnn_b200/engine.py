@@ -152,8 +152,8 @@ class Engine:
         return out
 
     # -- graph ------------------------------------------------------------------------------
-    def run_graph(self, data, plans, n_runs=None, row_subsets=None, uid_base=0, noise=None, init_params=None,
-                  want_trace=False, want_params=False, **kw):
+    def run_graph(self, data, plans, n_runs=None, row_subsets=None, uid_base=0, graph_uids=None, noise=None,
+                  init_params=None, want_trace=False, want_params=False, **kw):
         """Score every (candidate graph, run) instance.
 
         data: [n_rows_total, n_var] float32 (numpy or torch), columns as the plans' `col` indices.
@@ -185,11 +185,14 @@ class Engine:
             init_params = np.ascontiguousarray(init_params, np.float32)
             if init_params.size != n_inst * ld:
                 raise ValueError("init_params must be [n_inst, %d]" % ld)
+        guids = None if graph_uids is None else np.ascontiguousarray(graph_uids, np.uint64)
+        if guids is not None and guids.size != n_graphs:
+            raise ValueError("graph_uids must have one entry per graph")
         scores = np.empty((n_graphs, n_runs), np.float32)
         trace = np.empty((n_inst, epochs), np.float32) if want_trace else None
         pout = np.empty((n_inst, ld), np.float32) if want_params else None
         rc = self._lib.cgnn_b200_run_graph(self._h, C.byref(hp), _ptr(data), n_total, C.byref(gb.struct), n_runs,
-                                           _ptr(row_subsets), n_rows, C.c_ulonglong(int(uid_base)), _ptr(noise),
+                                           _ptr(row_subsets), n_rows, C.c_ulonglong(int(uid_base)), _ptr(guids), _ptr(noise),
                                            _ptr(init_params), ld, _ptr(scores), _ptr(trace), _ptr(pout))
         self._check(rc, "cgnn_b200_run_graph")
         return dict(scores=scores, trace=trace, params=pout)

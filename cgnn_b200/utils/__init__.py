@@ -1,1 +1,3 @@
 from .Settings import SETTINGS
+from .Formats import CCEPC_PairsFileReader
+from .Graph import DirectedGraph, UndirectedGraph

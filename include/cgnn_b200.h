@@ -160,6 +160,10 @@ typedef struct cgnn_graph_batch {
  *   data          [n_rows_total][n_var] fp32 row-major, columns in the order node_col refers to
  *   row_subsets   NULL (n_rows == n_rows_total, every instance sees all rows) or [n_inst][n_rows] row indices:
  *                 the per-call random subsample of CGNN.py:183-185, drawn by the caller
+ *   graph_uids    NULL, or [n_graphs] (host): Philox stream base of each graph; run r of graph g then uses
+ *                 stream graph_uids[g] + r instead of uid_base + g*n_runs + r.  The search drivers pass a
+ *                 hash of the graph structure, which makes a candidate's score independent of the batch
+ *                 it was evaluated in.
  *   noise         NULL (in-kernel Philox) or [n_inst][train+test epochs][n_noise_cols][n_rows]
  *   init_params   NULL (in-kernel N(0, init_std^2)) or [n_inst][ld_params]
  *   scores        out [n_graphs][n_runs]
@@ -169,7 +173,7 @@ int  cgnn_b200_run_graph(cgnn_ctx* ctx, const cgnn_hparams* hp,
                          const float* data, int n_rows_total,
                          const cgnn_graph_batch* graphs, int n_runs,
                          const int* row_subsets, int n_rows,
-                         unsigned long long uid_base,
+                         unsigned long long uid_base, const unsigned long long* graph_uids,
                          const float* noise, const float* init_params, int ld_params,
                          float* scores, float* loss_trace, float* params_out);
 
