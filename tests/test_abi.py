@@ -1,0 +1,52 @@
+"""The C-ABI shared library builds, loads and exports every symbol include/cgnn_b200.h declares
+(no compute calls here: there is no GPU in the CPU test run)."""
+import ctypes
+import os
+import re
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def declared_symbols():
+    text = open(os.path.join(ROOT, "include", "cgnn_b200.h")).read()
+    text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
+    return sorted(set(re.findall(r"\b(cgnn_b200_\w+)\s*\(", text)))
+
+
+def test_library_builds_and_exports_every_declared_symbol():
+    import __graft_entry__ as ge
+    ge.build()
+    from cgnn_b200 import _lib
+    lib = ctypes.CDLL(_lib.LIB_PATH)
+    names = declared_symbols()
+    assert len(names) >= 14
+    for n in names:
+        assert hasattr(lib, n), "libcgnn_b200.so does not export %s" % n
+    assert sorted(_lib.SYMBOLS) == names, "cgnn_b200/_lib.py must bind exactly the declared entry points"
+    assert lib.cgnn_b200_version() == 100
+
+
+def test_hparams_struct_layout_matches_header():
+    from cgnn_b200 import _lib
+    assert ctypes.sizeof(_lib.Hparams) == 40 and _lib.Hparams.seed.offset == 32
+    assert ctypes.sizeof(_lib.GraphBatchStruct) == 16 + 5 * 8
+
+
+def test_no_gpu_means_loud_failure():
+    """Without an sm_100 device the product raises; it never falls back to the oracle or the CPU."""
+    import torch
+    if torch.cuda.is_available():
+        return
+    import pytest
+    from cgnn_b200 import Engine, EngineError
+    with pytest.raises(EngineError):
+        Engine(0)
+
+
+def test_product_never_imports_the_oracle():
+    pkg = os.path.join(ROOT, "cgnn_b200")
+    for dirpath, _, files in os.walk(pkg):
+        for f in files:
+            if f.endswith((".py", ".cu", ".cuh", ".h")):
+                src = open(os.path.join(dirpath, f)).read()
+                assert not re.search(r"^\s*(from|import)\s+oracle\b", src, flags=re.M), "%s imports oracle" % f
