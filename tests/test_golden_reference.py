@@ -1,0 +1,70 @@
+"""Pins the oracle restatement against fixtures produced by the reference's OWN model code
+(Loss.py, GNN.py, CGNN.py, CGNN_confounders.py executed over oracle.tf1_shim by
+oracle/make_golden.py): same inputs, same noise -> same losses at every sess.run and the same
+.evaluate() mean, to fp64 round-off."""
+import os
+
+import numpy as np
+import pandas as pd
+
+GOLD = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+TIGHT = 1e-9
+
+
+def graph_from_fixture(z, mod):
+    skel = None
+    if len(z["skeleton"]):
+        skel = mod.UndirectedGraph(pd.DataFrame(z["skeleton"].tolist(), columns=["Cause", "Effect"]))
+    g = mod.DirectedGraph(skeleton=skel) if skel is not None else mod.DirectedGraph()
+    for (a, b), w in zip(z["edges"].tolist(), z["weights"].tolist()):
+        g.add(a, b, w)
+    return g
+
+
+def test_mmd_loss_and_gradient():
+    from oracle import mmd
+    z = np.load(os.path.join(GOLD, "ref_shim_mmd.npz"))
+    for k in range(3):
+        t, p = z["t%d" % k], z["p%d" % k]
+        loss, grad = mmd.mmd_loss_and_grad_autograd(t, p)
+        assert abs(loss - float(z["loss%d" % k])) < 1e-12 * abs(loss)
+        assert abs(mmd.mmd_loss_blocks(t, p) - float(z["loss%d" % k])) < TIGHT * abs(loss)
+        np.testing.assert_allclose(mmd.mmd_grad_analytic(t, p), z["grad%d" % k], rtol=0, atol=TIGHT * np.abs(z["grad%d" % k]).max())
+
+
+def test_pairwise_train_and_evaluate():
+    from oracle import gnn
+    z = np.load(os.path.join(GOLD, "ref_shim_pairwise.npz"))
+    for tag in ("a", "b"):
+        data, h, tr = z[tag + "_data"].astype(np.float64), int(z[tag + "_h"]), int(z[tag + "_train"])
+        theta, losses, _ = gnn.train(z[tag + "_theta0"], data, z[tag + "_noise"][:tr], h)
+        score, ev = gnn.evaluate(theta, data, z[tag + "_noise"][tr:], h)
+        np.testing.assert_allclose(np.concatenate([losses, ev]), z[tag + "_losses"], rtol=TIGHT)
+        assert abs(score - float(z[tag + "_score"])) < TIGHT * score
+
+
+def test_pairwise_both_directions():
+    """tf_run_instance (GNN.py:135-166): second model on the column-swapped data."""
+    from oracle import gnn
+    z = np.load(os.path.join(GOLD, "ref_shim_pairwise.npz"))
+    data, h, tr = z["c_data"].astype(np.float64), int(z["c_h"]), int(z["c_train"])
+    for d in range(2):
+        dd = np.ascontiguousarray(data[:, ::-1]) if d else data
+        s = gnn.run_instance(z["c_theta0"][d], dd, z["c_noise"][d, :tr], z["c_noise"][d, tr:], h)
+        assert abs(s - z["c_scores"][d]) < TIGHT * s
+
+
+def test_graph_and_confounder_models():
+    import cgnn_b200.utils.Graph as my_graph
+    from oracle import cgnn as oc
+    for name, conf in (("graph", False), ("confounders", True)):
+        z = np.load(os.path.join(GOLD, "ref_shim_%s.npz" % name))
+        g = graph_from_fixture(z, my_graph)
+        plan = oc.build_plan(g, confounders=conf)
+        assert plan["list_nodes"] == z["list_nodes"].tolist()
+        data, h, tr = z["data"].astype(np.float64), int(z["h"]), int(z["train"])
+        assert oc.n_params(plan, h) == z["theta0"].size
+        theta, losses, _ = oc.train(z["theta0"], data, z["noise"][:tr], plan, h)
+        score, ev = oc.evaluate(theta, data, z["noise"][tr:], plan, h)
+        np.testing.assert_allclose(np.concatenate([losses, ev]), z["losses"], rtol=TIGHT)
+        assert abs(score - float(z["score"])) < TIGHT * score
