@@ -7,7 +7,9 @@ MEMOISED RE-EXECUTION:
 
   1. run the algorithm on a copy of the start graph; `scorer(test_graph)` answers from a cache;
   2. on the first cache miss the run switches to speculation: the miss and every later request of
-     the current sweep are recorded and answered "+inf" (= move rejected, the common outcome);
+     the current sweep are recorded and answered NaN - every comparison with NaN is false, so the
+     move is rejected (the common outcome) and the 9999 "not evaluated" sentinel of the
+     hidden-variable search (CGNN_confounders.py:330,349) cannot win against it either;
      the run is abandoned at the end of that sweep;
   3. all recorded candidates are scored in ONE engine batch (candidates x runs instances), the cache
      is filled, and the algorithm is re-run from the start - host work only, microseconds;
@@ -80,7 +82,7 @@ class GraphScorer(object):
             return self.cache[key] + self.penalty(graph)
         if all(structure_key(g) != key for g in self.pending):
             self.pending.append(deepcopy(graph))
-        return float("inf")
+        return float("nan")
 
     def end_of_sweep(self):
         if self.pending is not None:

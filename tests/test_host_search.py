@@ -120,3 +120,30 @@ def test_search_accepts_some_moves(quiet):
     before = _edges(start)
     after = _edges(hill_climbing(start, _data(False), fake_fn, nb_runs=2))
     assert before != after
+
+
+def test_confounder_search_with_a_missing_edge_uses_the_add_branch(quiet, monkeypatch):
+    """Regression: while speculating, the 'not evaluated' sentinel 9999 (CGNN_confounders.py:330,349) must
+    not win the add decision - a start graph with a removed edge exercises that branch."""
+    import copy
+    import cgnn_b200.utils.Graph as my_graph
+    from cgnn_b200 import runtime
+    from cgnn_b200.CGNN_confounders import hill_climbing_confounders
+    monkeypatch.setattr(runtime, "get_engines", lambda: [FakeEngine()])
+    data = _data(True)
+    start = build_start(my_graph, True)
+    for a, b, _ in start.get_list_edges()[:4]:
+        g1 = copy.deepcopy(start)
+        g1.remove_edge(a, b)
+        g2 = copy.deepcopy(g1)
+        bat = hill_climbing_confounders(g1, data, nb_runs=2)
+        seq = hill_climbing_confounders(g2, data, fake_fn, nb_runs=2)
+        assert not bat.is_cyclic() and _edges(bat) == _edges(seq)
+        if refload.available():
+            import contextlib, io
+            ref = refload.load()
+            g3 = build_start(ref["Graph"], True)
+            g3.remove_edge(a, b)
+            with contextlib.redirect_stdout(io.StringIO()):
+                r = ref["CGNN_confounders"].hill_climbing_confounders(g3, data, fake_fn, nb_runs=2, nb_jobs=1)
+            assert _edges(r) == _edges(seq)
