@@ -78,6 +78,61 @@ __device__ __forceinline__ float ksum(float D) {
 }
 
 // ---------------------------------------------------------------------------------------------
+// "Primed" variants used by the pairwise kernel: coordinates are pre-multiplied by
+// S = sqrt(0.25*log2(e)), so the squared distance arrives as Dp = 0.25*log2(e)*D and
+//   exp(-gamma_g D) = ex2(Dp * A_g),  A_g = -gamma_g/0.25 = -0.02, -0.2, -1, -2, -4, -20, -200.
+// The gamma=0.25 kernel needs no multiply at all, gamma=50 is produced already weighted
+// (50*k6 = ex2(Dp*A6 + log2 50)), and the weighted sum is folded into Horner chains:
+//   wsum = 50 k6 + q (G0 + G1 q^9) + p (G2 + p (G3 + G4 p^2)) + G5 p^20      q = k(0.005), p = k(0.25)
+// ---------------------------------------------------------------------------------------------
+#define CGNN_PRESCALE 0.6005612043932249f          /* sqrt(0.25*log2(e)) */
+#define CGNN_LOG2_50  5.643856189774724f
+
+template <int POL>
+__device__ __forceinline__ float wsum_p(float Dp) {
+    const float q = ex2f(Dp * -0.02f);
+    const float p = ex2f(-Dp);
+    float w = ex2f(fmaf(Dp, -200.0f, CGNN_LOG2_50));             // 50 * k(50)
+    if (POL >= 2) {
+        const float q2 = q * q, q4 = q2 * q2, q8 = q4 * q4;
+        w = fmaf(fmaf(G1, q8 * q, G0), q, w);
+    } else {
+        w = fmaf(G1, ex2f(Dp * -0.2f), fmaf(G0, q, w));
+    }
+    if (POL >= 1) {
+        const float p2 = p * p;
+        w = fmaf(fmaf(p2 + G3, p, G2), p, w);                    // G2 p + G3 p^2 + p^4   (G4 == 1)
+        if (POL >= 3) { const float p4 = p2 * p2, p8 = p4 * p4; w = fmaf(G5, (p8 * p8) * p4, w); }
+        else w = fmaf(G5, ex2f(Dp * -20.0f), w);
+    } else {
+        w = fmaf(G2, p, w);
+        w = fmaf(G3, ex2f(Dp * -2.0f), w);
+        w += ex2f(Dp * -4.0f);
+        w = fmaf(G5, ex2f(Dp * -20.0f), w);
+    }
+    return w;
+}
+
+template <int POL>
+__device__ __forceinline__ float ksum_p(float Dp) {
+    const float q = ex2f(Dp * -0.02f);
+    const float p = ex2f(-Dp);
+    float s = ex2f(Dp * -200.0f);
+    if (POL >= 2) { const float q2 = q * q, q4 = q2 * q2, q5 = q4 * q; s += fmaf(q5, q5, q); }
+    else s += q + ex2f(Dp * -0.2f);
+    if (POL >= 1) {
+        const float p2 = p * p, p4 = p2 * p2;
+        float t = fmaf(p2, p2, p2) + p;                          // p + p^2 + p^4
+        if (POL >= 3) { const float p8 = p4 * p4; t = fmaf(p8 * p8, p4, t); }
+        else t += ex2f(Dp * -20.0f);
+        s += t;
+    } else {
+        s += (p + ex2f(Dp * -2.0f)) + (ex2f(Dp * -4.0f) + ex2f(Dp * -20.0f));
+    }
+    return s;
+}
+
+// ---------------------------------------------------------------------------------------------
 // Philox4x32-10 counter RNG + Box-Muller.  Engine-defined streams (the reference is unseeded):
 //   key     = (seed_lo, seed_hi)
 //   counter = (index, step, stream, instance uid)     -> 4 x 32 random bits -> 4 normals

@@ -9,30 +9,38 @@
 //                                             PP taken once per unordered pair, direct differences
 //
 // Data layout (all in shared memory for the instance's whole life; HBM is touched once at
-// instance start and once at the end):
-//   Tc[NP] float2 = (x_j, y_j)      observed pair, cause first        NP = 32*ceil(N/32)
-//   Pc[NP] float2 = (x_j, yhat_j)   generated pair (cause column copied, GNN.py:70-72)
-//   es[NP] float  = noise e_j of the current step (needed again by the backward pass)
-//   g64[NP] int64 = fixed-point accumulator of dLoss/d yhat_j (unscaled)
+// instance start and once at the end).  Coordinates are pre-multiplied by S = sqrt(0.25*log2 e)
+// (common.cuh, "primed" kernels) and kept as one float4 per row,
+//   Q[j] = (S x_j, S y_j, S yhat_j, 0)      x = cause (copied into the generated pair, GNN.py:70-72)
+// in a DOUBLED-TILE layout: rows are cut into tiles of 32 and every tile is stored twice in a row,
+// Qd[64 J + t] = Q[32 J + (t & 31)], t = 0..63.  Lane l then reaches "its" column of step s,
+// (l + s) & 31, at the fixed offset l + s: the skewed walk needs no index arithmetic at all.
+//   xs[NP], es[NP], yh[NP]  unscaled cause, current noise and generated value (generator phases)
+//   g64[NP] int64           fixed-point accumulator of dLoss/d yhat (primed, unscaled)
 //   padded rows hold x = 1e15 so that every kernel value against them is exactly 0.
 //
-// MMD mapping: lane <-> row i of a 32-row block, columns streamed from shared memory.
-//   PT (pred x true)  : broadcast loads of Tc[j]; row accumulator only (T has no gradient)
-//   PP off-diagonal   : block pair (I,J) visited once; lane l meets column (l+s)&31 at step s
-//                       (conflict-free skewed loads); the column-side gradient rides in a register
-//                       that is rotated with one shuffle per evaluation; after 32 steps lane l owns
-//                       column l's total, flushed with one fixed-point shared atomic
-//   PP diagonal block : plain broadcast form (0.7 % of the evaluations)
-// Each evaluation = dx,dy,D (4 FP32) + 7 kernels (MUFU ex2) + weights (8 FP32) + 1-2 FFMA.
+// MMD mapping ("trio"): for an unordered pair of DIFFERENT tiles (I, J), lane l owns row i = 32 I + l
+// and meets column j = 32 J + ((l+s)&31) at step s.  The three kernel evaluations that involve the
+// two rows - PP(i,j), PT(i,j) and PT(j,i) - share (x_i - x_j)^2, which is therefore computed once
+// per three evaluations; the column-side gradient (from PP and from PT(j,i)) rides in ONE register
+// that is rotated with one shuffle per step, so after 32 steps lane l owns column l's total, flushed
+// with one fixed-point shared atomic.  Diagonal tiles use a "duo" walk (PP(i,j), PT(i,j)) over all
+// ordered pairs.  Per evaluation: ~25 issue slots of which 3-7 MUFU (policy dependent).
 #pragma once
 #include "common.cuh"
 
 namespace cgnn {
 
-constexpr int PW_NT = 512;              // threads per CTA
+#ifndef CGNN_PW_NT
+#define CGNN_PW_NT 512
+#endif
+#ifndef CGNN_PW_CTAS
+#define CGNN_PW_CTAS 2
+#endif
+constexpr int PW_NT = CGNN_PW_NT;       // threads per CTA
 constexpr int PW_NW = PW_NT / 32;       // warps per CTA
-constexpr int PW_MIN_CTAS = 2;          // persistent CTAs per SM
-constexpr int PW_MAX_ROWS = 4 * PW_NT;  // one 4-row quad per thread in the generator phases
+constexpr int PW_MIN_CTAS = CGNN_PW_CTAS;
+constexpr int PW_MAX_ROWS = 2048;
 constexpr float PW_PAD = 1.0e15f;
 
 struct PairwiseArgs {
@@ -55,7 +63,7 @@ struct PairwiseArgs {
 };
 
 struct PwSmem {
-    float2* Tc; float2* Pc; float* es; long long* g64;
+    float4* Qd; float* xs; float* es; float* yh; long long* g64;
     float* theta; float* am; float* av; float* part; double* red;
     int part_stride;
 };
@@ -65,121 +73,134 @@ __host__ __device__ inline size_t pw_smem_bytes(int np_max, int h) {
     int P = 4 * h + 1;
     int Pp = (P + 3) & ~3;
     size_t b = 0;
-    b += size_t(np_max) * 8 * 2;                 // Tc, Pc
+    b += size_t(np_max) * 2 * 16;                // Qd (doubled tiles)
     b += size_t(np_max) * 8;                     // g64
-    b += size_t(np_max) * 4;                     // es
+    b += size_t(PW_NW + 4) * 8;                  // red[], TT, beta1^t, beta2^t, lr_t
+    b += size_t(np_max) * 4 * 3;                 // xs, es, yh
     b += size_t(Pp) * 4 * 3;                     // theta, m, v
     b += size_t(PW_NW) * (nchunk * 32 + 4) * 4;  // per-warp partial gradient sums
-    b += size_t(PW_NW + 4) * 8;                  // red[], TT, beta1^t, beta2^t, lr_t
     return (b + 15) & ~size_t(15);
 }
 
+// position of row i in the doubled-tile layout (first copy; the second is +32)
+__device__ __forceinline__ int pw_slot_of_row(int i) { return ((i >> 5) << 6) + (i & 31); }
+
 // ---- unit partition -------------------------------------------------------------------------
-// Row block I owns nPT broadcast tiles (PT), one diagonal tile and nPP(I) off-diagonal PP tiles
-// J = (I+1+q) mod NB.  For odd NB every block has (NB-1)/2 of them; for even NB the antipodal
-// pair (I, I+NB/2) is given to the lower I.  Units are flattened I-major and dealt to the warps
-// in equal contiguous ranges, so a warp changes row block at most a few times per pass.
+// Row block I owns its diagonal tile and npp(I) off-diagonal tiles J = (I+1+q) mod NB.  For odd NB
+// every block has (NB-1)/2 of them; for even NB the antipodal pair (I, I+NB/2) goes to the lower I.
+// Units are flattened I-major and dealt to the warps in equal contiguous ranges.
 __device__ __forceinline__ int pw_npp(int I, int NB) {
     return (NB & 1) ? (NB - 1) / 2 : (NB / 2 - 1 + (I < NB / 2 ? 1 : 0));
 }
 
-// Broadcast-column tile, gradient form: returns sum_j w(i,j) * (yi - col[j].y).
+// Off-diagonal tile pair, gradient form.  tile = &Qd[64 J + lane].  Returns the row-side sum for row i;
+// colsum receives the total for column 32 J + lane (both in primed units, unscaled).
 template <int POL>
-__device__ __forceinline__ float bc_train(float xi, float yi, const float2* __restrict__ col, int j0, int j1) {
-    float acc = 0.f;
-#pragma unroll 4
-    for (int j = j0; j < j1; ++j) {
-        const float2 c = col[j];
-        const float dx = xi - c.x, dy = yi - c.y;
-        const float D = fmaf(dy, dy, dx * dx);
-        acc = fmaf(wsum<POL>(D), dy, acc);
-    }
-    return acc;
-}
-
-// Broadcast-column tile, loss form: returns sum_j sum_g k_g(i,j).
-template <int POL>
-__device__ __forceinline__ float bc_eval(float xi, float yi, const float2* __restrict__ col, int j0, int j1) {
-    float acc = 0.f;
-#pragma unroll 4
-    for (int j = j0; j < j1; ++j) {
-        const float2 c = col[j];
-        const float dx = xi - c.x, dy = yi - c.y;
-        const float D = fmaf(dy, dy, dx * dx);
-        acc += ksum<POL>(D);
-    }
-    return acc;
-}
-
-// Off-diagonal PP tile, gradient form, each unordered pair once.  Returns the row-side sum
-// sum_j w (yi - yj); colsum receives, for column J0+lane, sum_i w (yi - yj) over the 32 rows.
-template <int POL>
-__device__ __forceinline__ float pp_sym_train(float xi, float yi, const float2* __restrict__ Pc, int J0, int lane,
-                                              float& colsum) {
+__device__ __forceinline__ float trio_train(float xi, float yi, float yhi, const float4* __restrict__ tile, int lane,
+                                            float& colsum) {
     float ra = 0.f, ca = 0.f;
     const int src = (lane + 1) & 31;
-#pragma unroll 8
+#pragma unroll 4
     for (int s = 0; s < 32; ++s) {
-        const float2 c = Pc[J0 + ((lane + s) & 31)];
-        const float dx = xi - c.x, dy = yi - c.y;
-        const float D = fmaf(dy, dy, dx * dx);
-        const float t = wsum<POL>(D) * dy;
-        ra += t;
-        ca += t;
+        const float4 c = tile[s];
+        const float dx = xi - c.x;
+        const float dx2 = dx * dx;
+        const float a = yhi - c.z;      // PP(i,j):  yhat_i - yhat_j
+        const float b = yhi - c.y;      // PT(i,j):  yhat_i - y_j
+        const float d = c.z - yi;       // PT(j,i):  yhat_j - y_i
+        const float wpp = wsum_p<POL>(fmaf(a, a, dx2));
+        const float w1 = wsum_p<POL>(fmaf(b, b, dx2));
+        const float w2 = wsum_p<POL>(fmaf(d, d, dx2));
+        ra = fmaf(w1, b, ra);
+        ra = fmaf(-wpp, a, ra);
+        ca = fmaf(wpp, a, ca);
+        ca = fmaf(w2, d, ca);
         ca = __shfl_sync(0xffffffffu, ca, src);
     }
     colsum = ca;
     return ra;
 }
 
+// Diagonal tile, gradient form: all ordered pairs of the tile, row side only.
+template <int POL>
+__device__ __forceinline__ float duo_train(float xi, float yhi, const float4* __restrict__ tile) {
+    float ra = 0.f;
+#pragma unroll 4
+    for (int s = 0; s < 32; ++s) {
+        const float4 c = tile[s];
+        const float dx = xi - c.x;
+        const float dx2 = dx * dx;
+        const float a = yhi - c.z, b = yhi - c.y;
+        ra = fmaf(wsum_p<POL>(fmaf(b, b, dx2)), b, ra);
+        ra = fmaf(-wsum_p<POL>(fmaf(a, a, dx2)), a, ra);
+    }
+    return ra;
+}
+
+// Loss forms: kPP - kPT(i,j) - kPT(j,i) per unordered pair (to be doubled), kPP - 2 kPT per ordered pair.
+template <int POL>
+__device__ __forceinline__ float trio_eval(float xi, float yi, float yhi, const float4* __restrict__ tile) {
+    float acc = 0.f;
+#pragma unroll 4
+    for (int s = 0; s < 32; ++s) {
+        const float4 c = tile[s];
+        const float dx = xi - c.x;
+        const float dx2 = dx * dx;
+        const float a = yhi - c.z, b = yhi - c.y, d = c.z - yi;
+        acc += ksum_p<POL>(fmaf(a, a, dx2)) - (ksum_p<POL>(fmaf(b, b, dx2)) + ksum_p<POL>(fmaf(d, d, dx2)));
+    }
+    return acc;
+}
+template <int POL>
+__device__ __forceinline__ float duo_eval(float xi, float yhi, const float4* __restrict__ tile) {
+    float acc = 0.f;
+#pragma unroll 4
+    for (int s = 0; s < 32; ++s) {
+        const float4 c = tile[s];
+        const float dx = xi - c.x;
+        const float dx2 = dx * dx;
+        const float a = yhi - c.z, b = yhi - c.y;
+        acc += fmaf(-2.f, ksum_p<POL>(fmaf(b, b, dx2)), ksum_p<POL>(fmaf(a, a, dx2)));
+    }
+    return acc;
+}
+
 // One MMD pass over an instance.
-//   TRAIN: accumulates the unscaled dLoss/d yhat into g64 (rows: +PT - PP; columns of PP tiles: +)
-//   else : returns this lane's share of  PP - 2 PT  (or of the full PP when ptA == nullptr: used for TT)
+//   TRAIN: accumulates the primed, unscaled dLoss/d yhat into g64
+//   else : returns this lane's share of  PP - 2 PT
 template <int POL, bool TRAIN>
-__device__ double mmd_pass(const float2* __restrict__ rowA, const float2* __restrict__ ptA,
-                           const float2* __restrict__ ppA, long long* g64, int N, int NB, int warp, int lane) {
-    const int nPT = ptA ? NB : 0;
+__device__ double mmd_pass(const float4* __restrict__ Qd, long long* g64, int N, int NB, int warp, int lane) {
     int total = 0;
-    for (int I = 0; I < NB; ++I) total += nPT + 1 + pw_npp(I, NB);
+    for (int I = 0; I < NB; ++I) total += 1 + pw_npp(I, NB);
     const int lo = int((long long)warp * total / PW_NW);
     const int hi = int((long long)(warp + 1) * total / PW_NW);
     int I = 0, base = 0;
-    while (I < NB && base + nPT + 1 + pw_npp(I, NB) <= lo) { base += nPT + 1 + pw_npp(I, NB); ++I; }
+    while (I < NB && base + 1 + pw_npp(I, NB) <= lo) { base += 1 + pw_npp(I, NB); ++I; }
     double lsum = 0.0;
     int u = lo;
     while (u < hi) {
-        const int UI = nPT + 1 + pw_npp(I, NB);
+        const int UI = 1 + pw_npp(I, NB);
         const int a0 = u - base;
         const int b0 = min(hi - base, UI);
         const int i = 32 * I + lane;
-        const float2 me = rowA[i];
-        const float xi = me.x, yi = me.y;
+        const float4 me = Qd[64 * I + lane];
         double acc = 0.0;
-        // PT tiles a0 .. min(b0, nPT)
-        if (a0 < nPT) {
-            const int j1 = min(32 * min(b0, nPT), N);
-            for (int jc = 32 * a0; jc < j1; jc += 64) {
-                const int je = min(jc + 64, j1);
-                if (TRAIN) acc += double(bc_train<POL>(xi, yi, ptA, jc, je));
-                else       acc -= 2.0 * double(bc_eval<POL>(xi, yi, ptA, jc, je));
-            }
-        }
-        // diagonal tile
-        if (a0 <= nPT && b0 > nPT) {
-            const int je = min(32 * I + 32, N);
-            if (TRAIN) acc -= double(bc_train<POL>(xi, yi, ppA, 32 * I, je));
-            else       acc += double(bc_eval<POL>(xi, yi, ppA, 32 * I, je));
-        }
-        // off-diagonal PP tiles
-        for (int q = max(a0, nPT + 1) - (nPT + 1); q < b0 - (nPT + 1); ++q) {
-            int J = I + 1 + q;
-            if (J >= NB) J -= NB;
-            if (TRAIN) {
-                float cs;
-                acc -= double(pp_sym_train<POL>(xi, yi, ppA, 32 * J, lane, cs));
-                if (32 * J + lane < N) fx_add(&g64[32 * J + lane], double(cs));
+        for (int q = a0; q < b0; ++q) {
+            if (q == 0) {
+                const float4* tile = Qd + 64 * I + lane;
+                if (TRAIN) acc += double(duo_train<POL>(me.x, me.z, tile));
+                else       acc += double(duo_eval<POL>(me.x, me.z, tile));
             } else {
-                acc += 2.0 * double(bc_eval<POL>(xi, yi, ppA, 32 * J, min(32 * J + 32, N)));
+                int J = I + q;
+                if (J >= NB) J -= NB;
+                const float4* tile = Qd + 64 * J + lane;
+                if (TRAIN) {
+                    float cs;
+                    acc += double(trio_train<POL>(me.x, me.y, me.z, tile, lane, cs));
+                    if (32 * J + lane < N) fx_add(&g64[32 * J + lane], double(cs));
+                } else {
+                    acc += 2.0 * double(trio_eval<POL>(me.x, me.y, me.z, tile));
+                }
             }
         }
         if (TRAIN) { if (i < N) fx_add(&g64[i], acc); }
@@ -187,6 +208,28 @@ __device__ double mmd_pass(const float2* __restrict__ rowA, const float2* __rest
         u = base + b0;
         base += UI;
         ++I;
+    }
+    return lsum;
+}
+
+// TT = sum_ij sum_g k(T_i, T_j): once per instance, plain row x all-columns walk (broadcast loads).
+template <int POL>
+__device__ double tt_pass(const float4* __restrict__ Qd, int N, int NB, int warp, int lane) {
+    double lsum = 0.0;
+    for (int I = warp; I < NB; I += PW_NW) {
+        const float4 me = Qd[64 * I + lane];
+        double acc = 0.0;
+        for (int J = 0; J < NB; ++J) {
+            float part = 0.f;
+#pragma unroll 4
+            for (int t = 0; t < 32; ++t) {
+                const float4 c = Qd[64 * J + t];
+                const float dx = me.x - c.x, dy = me.y - c.y;
+                part += ksum_p<POL>(fmaf(dy, dy, dx * dx));
+            }
+            acc += double(part);
+        }
+        if (32 * I + lane < N) lsum += acc;
     }
     return lsum;
 }
@@ -204,76 +247,87 @@ __device__ __forceinline__ double block_sum(double v, double* red, int warp, int
     return t;
 }
 
-// Generator forward for this thread's 4-row quad (GNN.py:64-67), noise from Philox or the caller.
-__device__ __forceinline__ void pw_forward(const PwSmem& s, const PairwiseArgs& a, int N, int h, int step,
+// Generator forward for 4-row quads (GNN.py:64-67), noise from Philox or the caller.
+__device__ __forceinline__ void pw_forward(const PwSmem& s, const PairwiseArgs& a, int N, int NP, int h, int step,
                                            unsigned int uid, const float* noise_row, int tid) {
-    const int r0 = 4 * tid;
-    if (r0 < ((N + 31) & ~31)) {   // zero the gradient accumulators of this quad (padded rows too)
+    for (int q = tid; 4 * q < NP; q += PW_NT) {
+        const int r0 = 4 * q;
         s.g64[r0] = 0; s.g64[r0 + 1] = 0; s.g64[r0 + 2] = 0; s.g64[r0 + 3] = 0;
-    }
-    if (r0 >= N) return;
-    float e[4];
-    if (noise_row) {
+        if (r0 >= N) continue;
+        float e[4];
+        if (noise_row) {
 #pragma unroll
-        for (int r = 0; r < 4; ++r) e[r] = (r0 + r < N) ? noise_row[r0 + r] : 0.f;
-    } else {
-        const float4 n = normal4(philox4x32_10(make_uint4(tid, step, STREAM_NOISE, uid), a.key));
-        e[0] = n.x; e[1] = n.y; e[2] = n.z; e[3] = n.w;
-    }
-    float x[4], y[4];
-    const float bout = s.theta[4 * h];
-#pragma unroll
-    for (int r = 0; r < 4; ++r) { x[r] = s.Tc[r0 + r].x; y[r] = bout; }
-    for (int k = 0; k < h; ++k) {
-        const float w0 = s.theta[k], w1 = s.theta[h + k], b = s.theta[2 * h + k], wo = s.theta[3 * h + k];
-#pragma unroll
-        for (int r = 0; r < 4; ++r) {
-            const float z = fmaf(x[r], w0, fmaf(e[r], w1, b));
-            y[r] = fmaf(fmaxf(z, 0.f), wo, y[r]);
+            for (int r = 0; r < 4; ++r) e[r] = (r0 + r < N) ? noise_row[r0 + r] : 0.f;
+        } else {
+            const float4 n = normal4(philox4x32_10(make_uint4(q, step, STREAM_NOISE, uid), a.key));
+            e[0] = n.x; e[1] = n.y; e[2] = n.z; e[3] = n.w;
         }
-    }
+        float x[4], y[4];
+        const float bout = s.theta[4 * h];
 #pragma unroll
-    for (int r = 0; r < 4; ++r)
-        if (r0 + r < N) { s.Pc[r0 + r].y = y[r]; s.es[r0 + r] = e[r]; }
+        for (int r = 0; r < 4; ++r) { x[r] = s.xs[r0 + r]; y[r] = bout; }
+        for (int k = 0; k < h; ++k) {
+            const float w0 = s.theta[k], w1 = s.theta[h + k], b = s.theta[2 * h + k], wo = s.theta[3 * h + k];
+#pragma unroll
+            for (int r = 0; r < 4; ++r) {
+                const float z = fmaf(x[r], w0, fmaf(e[r], w1, b));
+                y[r] = fmaf(fmaxf(z, 0.f), wo, y[r]);
+            }
+        }
+#pragma unroll
+        for (int r = 0; r < 4; ++r)
+            if (r0 + r < N) {
+                const int sl = pw_slot_of_row(r0 + r);
+                const float yp = CGNN_PRESCALE * y[r];
+                s.Qd[sl].z = yp; s.Qd[sl + 32].z = yp;
+                s.es[r0 + r] = e[r]; s.yh[r0 + r] = y[r];
+            }
+    }
 }
 
 // Generator backward: per-warp partial parameter gradients into s.part (deterministic tree).
-__device__ __forceinline__ void pw_backward_partials(const PwSmem& s, int N, int h, int tid, int warp, int lane) {
-    const int r0 = 4 * tid;
-    const float scale = 4.0f / (float(N) * float(N));
-    float x[4], e[4], d[4];
-#pragma unroll
-    for (int r = 0; r < 4; ++r) {
-        const bool ok = r0 + r < N;
-        x[r] = ok ? s.Tc[r0 + r].x : 0.f;
-        e[r] = ok ? s.es[r0 + r] : 0.f;
-        d[r] = ok ? float(fx_get(&s.g64[r0 + r])) * scale : 0.f;
-    }
+__device__ __forceinline__ void pw_backward_partials(const PwSmem& s, int N, int NP, int h, int tid, int warp, int lane) {
+    const float scale = 4.0f / (float(N) * float(N) * CGNN_PRESCALE);
     const int nchunk = (h + 7) >> 3;
     float* mine = s.part + warp * s.part_stride;
-    for (int c = 0; c < nchunk; ++c) {
-        float v[32];
+    for (int c = 0; c < nchunk; ++c) mine[32 * c + lane] = 0.f;
+    __syncwarp();
+    float sd_tot = 0.f;
+    for (int q0 = 0; 4 * q0 < NP; q0 += PW_NT) {          // whole warps iterate together (uniform trip count)
+        const int r0 = 4 * (q0 + tid);
+        float x[4], e[4], d[4];
 #pragma unroll
-        for (int kk = 0; kk < 8; ++kk) {
-            const int k = 8 * c + kk;
-            float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
-            if (k < h) {
-                const float w0 = s.theta[k], w1 = s.theta[h + k], b = s.theta[2 * h + k], wo = s.theta[3 * h + k];
-#pragma unroll
-                for (int r = 0; r < 4; ++r) {
-                    const float z = fmaf(x[r], w0, fmaf(e[r], w1, b));
-                    const float dz = z > 0.f ? d[r] * wo : 0.f;
-                    s0 = fmaf(x[r], dz, s0);
-                    s1 = fmaf(e[r], dz, s1);
-                    s2 += dz;
-                    s3 = fmaf(fmaxf(z, 0.f), d[r], s3);
-                }
-            }
-            v[4 * kk] = s0; v[4 * kk + 1] = s1; v[4 * kk + 2] = s2; v[4 * kk + 3] = s3;
+        for (int r = 0; r < 4; ++r) {
+            const bool ok = r0 + r < N;
+            x[r] = ok ? s.xs[r0 + r] : 0.f;
+            e[r] = ok ? s.es[r0 + r] : 0.f;
+            d[r] = ok ? float(fx_get(&s.g64[r0 + r])) * scale : 0.f;
         }
-        mine[32 * c + lane] = warp_reduce32(v, lane);
+        for (int c = 0; c < nchunk; ++c) {
+            float v[32];
+#pragma unroll
+            for (int kk = 0; kk < 8; ++kk) {
+                const int k = 8 * c + kk;
+                float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
+                if (k < h) {
+                    const float w0 = s.theta[k], w1 = s.theta[h + k], b = s.theta[2 * h + k], wo = s.theta[3 * h + k];
+#pragma unroll
+                    for (int r = 0; r < 4; ++r) {
+                        const float z = fmaf(x[r], w0, fmaf(e[r], w1, b));
+                        const float dz = z > 0.f ? d[r] * wo : 0.f;
+                        s0 = fmaf(x[r], dz, s0);
+                        s1 = fmaf(e[r], dz, s1);
+                        s2 += dz;
+                        s3 = fmaf(fmaxf(z, 0.f), d[r], s3);
+                    }
+                }
+                v[4 * kk] = s0; v[4 * kk + 1] = s1; v[4 * kk + 2] = s2; v[4 * kk + 3] = s3;
+            }
+            mine[32 * c + lane] += warp_reduce32(v, lane);
+        }
+        sd_tot += (d[0] + d[1]) + (d[2] + d[3]);
     }
-    const float sd = warp_sum((d[0] + d[1]) + (d[2] + d[3]));
+    const float sd = warp_sum(sd_tot);
     if (lane == 0) mine[32 * nchunk] = sd;
 }
 
@@ -295,11 +349,12 @@ __global__ void __launch_bounds__(PW_NT, PW_MIN_CTAS) pairwise_kernel(const Pair
     PwSmem s;
     {
         unsigned char* p = smem_raw;
-        s.Tc = reinterpret_cast<float2*>(p);      p += size_t(a.np_max) * 8;
-        s.Pc = reinterpret_cast<float2*>(p);      p += size_t(a.np_max) * 8;
+        s.Qd = reinterpret_cast<float4*>(p);      p += size_t(a.np_max) * 32;
         s.g64 = reinterpret_cast<long long*>(p);  p += size_t(a.np_max) * 8;
         s.red = reinterpret_cast<double*>(p);     p += size_t(PW_NW + 4) * 8;
+        s.xs = reinterpret_cast<float*>(p);       p += size_t(a.np_max) * 4;
         s.es = reinterpret_cast<float*>(p);       p += size_t(a.np_max) * 4;
+        s.yh = reinterpret_cast<float*>(p);       p += size_t(a.np_max) * 4;
         s.theta = reinterpret_cast<float*>(p);    p += size_t(Pp) * 4;
         s.am = reinterpret_cast<float*>(p);       p += size_t(Pp) * 4;
         s.av = reinterpret_cast<float*>(p);       p += size_t(Pp) * 4;
@@ -323,34 +378,37 @@ __global__ void __launch_bounds__(PW_NT, PW_MIN_CTAS) pairwise_kernel(const Pair
         const int epochs = a.train_epochs + a.test_epochs;
         const float* noise = a.noise ? a.noise + size_t(out) * epochs * a.ld_rows : nullptr;
 
-        // ---- load the pair (cause first), pad ---------------------------------------------
+        // ---- load the pair (cause first), prescale, pad, duplicate every tile -------------------
         for (int i = tid; i < NP; i += PW_NT) {
-            float2 t = make_float2(PW_PAD, 0.f);
+            float4 t = make_float4(PW_PAD, 0.f, 0.f, 0.f);
+            float x = 0.f;
             if (i < N) {
                 const float2 v = reinterpret_cast<const float2*>(src)[i];
-                t = dir ? make_float2(v.y, v.x) : v;
+                x = dir ? v.y : v.x;
+                const float y = dir ? v.x : v.y;
+                t = make_float4(CGNN_PRESCALE * x, CGNN_PRESCALE * y, 0.f, 0.f);
             }
-            s.Tc[i] = t;
-            s.Pc[i] = make_float2(t.x, 0.f);
-            s.es[i] = 0.f;
+            const int sl = pw_slot_of_row(i);
+            s.Qd[sl] = t; s.Qd[sl + 32] = t;
+            s.xs[i] = x; s.es[i] = 0.f; s.yh[i] = 0.f;
         }
         // ---- parameters (GNN.py:21-29, 55-58) and Adam state -------------------------------
-        if (tid < Pp) {
+        for (int p = tid; p < Pp; p += PW_NT) {
             float th = 0.f;
-            if (tid < P) {
-                if (a.init_params) th = a.init_params[size_t(out) * P + tid];
+            if (p < P) {
+                if (a.init_params) th = a.init_params[size_t(out) * P + p];
                 else {
-                    const float4 n = normal4(philox4x32_10(make_uint4(tid >> 2, 0u, STREAM_INIT, uid), a.key));
-                    const int e = tid & 3;
+                    const float4 n = normal4(philox4x32_10(make_uint4(p >> 2, 0u, STREAM_INIT, uid), a.key));
+                    const int e = p & 3;
                     th = a.init_std * (e == 0 ? n.x : e == 1 ? n.y : e == 2 ? n.z : n.w);
                 }
             }
-            s.theta[tid] = th; s.am[tid] = 0.f; s.av[tid] = 0.f;
+            s.theta[p] = th; s.am[p] = 0.f; s.av[p] = 0.f;
         }
         __syncthreads();
         // ---- TT: constant per instance, fp64 accumulation ----------------------------------
         {
-            const double part = mmd_pass<POL, false>(s.Tc, nullptr, s.Tc, nullptr, N, NB, warp, lane);
+            const double part = tt_pass<POL>(s.Qd, N, NB, warp, lane);
             const double tt = block_sum(part, s.red, warp, lane);
             if (tid == 0) s_TT = tt;
         }
@@ -367,11 +425,11 @@ __global__ void __launch_bounds__(PW_NT, PW_MIN_CTAS) pairwise_kernel(const Pair
                 s.red[PW_NW + 1] = b1p; s.red[PW_NW + 2] = b2p;
                 s.red[PW_NW + 3] = double(a.lr) * sqrt(1.0 - b2p) / (1.0 - b1p);
             }
-            pw_forward(s, a, N, h, it, uid, noise ? noise + size_t(it) * a.ld_rows : nullptr, tid);
+            pw_forward(s, a, N, NP, h, it, uid, noise ? noise + size_t(it) * a.ld_rows : nullptr, tid);
             __syncthreads();
             const bool traced = a.dbg_loss || (a.trace && a.trace_every > 0 && it % a.trace_every == 0);
             if (traced) {   // loss fetched with the train op is the pre-update loss (GNN.py:93-94)
-                const double part = mmd_pass<POL, false>(s.Pc, s.Tc, s.Pc, nullptr, N, NB, warp, lane);
+                const double part = mmd_pass<POL, false>(s.Qd, nullptr, N, NB, warp, lane);
                 const double sum = block_sum(part, s.red, warp, lane);
                 if (tid == 0) {
                     const float loss = float((sum + s_TT) * invN2);
@@ -381,39 +439,40 @@ __global__ void __launch_bounds__(PW_NT, PW_MIN_CTAS) pairwise_kernel(const Pair
             } else if (a.trace && tid == 0) {
                 a.trace[size_t(out) * epochs + it] = __int_as_float(0x7fc00000);
             }
-            if (a.dbg_yhat) for (int i = tid; i < N; i += PW_NT) a.dbg_yhat[size_t(it) * N + i] = s.Pc[i].y;
-            mmd_pass<POL, true>(s.Pc, s.Tc, s.Pc, s.g64, N, NB, warp, lane);
+            if (a.dbg_yhat) for (int i = tid; i < N; i += PW_NT) a.dbg_yhat[size_t(it) * N + i] = s.yh[i];
+            mmd_pass<POL, true>(s.Qd, s.g64, N, NB, warp, lane);
             __syncthreads();
             if (a.dbg_dldy) {
-                const float scale = 4.0f / (float(N) * float(N));
+                const float scale = 4.0f / (float(N) * float(N) * CGNN_PRESCALE);
                 for (int i = tid; i < N; i += PW_NT) a.dbg_dldy[size_t(it) * N + i] = float(fx_get(&s.g64[i])) * scale;
             }
-            pw_backward_partials(s, N, h, tid, warp, lane);
+            pw_backward_partials(s, N, NP, h, tid, warp, lane);
             __syncthreads();
-            if (tid < P) {
-                const int slot = pw_slot(tid, h);
+            for (int p = tid; p < P; p += PW_NT) {
+                const int slot = pw_slot(p, h);
                 float g = 0.f;
 #pragma unroll
                 for (int w = 0; w < PW_NW; ++w) g += s.part[w * s.part_stride + slot];
                 const float lr_t = float(s.red[PW_NW + 3]);
-                float m = s.am[tid], v = s.av[tid];
-                const float th = adam_update(s.theta[tid], g, m, v, lr_t);
-                s.am[tid] = m; s.av[tid] = v; s.theta[tid] = th;
-                if (a.dbg_grad) a.dbg_grad[size_t(it) * P + tid] = g;
-                if (a.dbg_params) a.dbg_params[size_t(it) * P + tid] = th;
+                float m = s.am[p], v = s.av[p];
+                const float th = adam_update(s.theta[p], g, m, v, lr_t);
+                s.am[p] = m; s.av[p] = v; s.theta[p] = th;
+                if (a.dbg_grad) a.dbg_grad[size_t(it) * P + p] = g;
+                if (a.dbg_params) a.dbg_params[size_t(it) * P + p] = th;
             }
         }
         __syncthreads();
-        if (a.params_out && tid < P) a.params_out[size_t(out) * P + tid] = s.theta[tid];
+        if (a.params_out)
+            for (int p = tid; p < P; p += PW_NT) a.params_out[size_t(out) * P + p] = s.theta[p];
 
         // ---- evaluation (GNN.py:115-126): mean of test_epochs fresh-noise losses ---------------
         double score_sum = 0.0;
         for (int it = 0; it < a.test_epochs; ++it) {
             __syncthreads();
-            pw_forward(s, a, N, h, a.train_epochs + it, uid,
+            pw_forward(s, a, N, NP, h, a.train_epochs + it, uid,
                        noise ? noise + size_t(a.train_epochs + it) * a.ld_rows : nullptr, tid);
             __syncthreads();
-            const double part = mmd_pass<POL, false>(s.Pc, s.Tc, s.Pc, nullptr, N, NB, warp, lane);
+            const double part = mmd_pass<POL, false>(s.Qd, nullptr, N, NB, warp, lane);
             const double sum = block_sum(part, s.red, warp, lane);
             if (tid == 0) {
                 const float loss = float((sum + s_TT) * invN2);    // the reference fetches an fp32 loss ...
