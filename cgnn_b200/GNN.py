@@ -30,6 +30,18 @@ def _subsample_runs(m, n_runs, uid):
     return out
 
 
+def _staging(shape):
+    """Zeroed float32 host batch buffer; page-locked when a CUDA runtime is present so that the engine's
+    H2D copy is a true asynchronous DMA."""
+    try:
+        import torch
+        if torch.cuda.is_available():
+            return torch.zeros(shape, dtype=torch.float32).pin_memory().numpy()
+    except Exception:
+        pass
+    return np.zeros(shape, np.float32)
+
+
 def score_pairs(pairs, idx0=0, **kwargs):
     """Per-run direction scores of a list of [N,2] float32 matrices: array [n_pairs, nb_runs, 2]
     (A->B, B->A).  The batched replacement of `[tf_run_instance(m, idx, run) for run in range(nb_runs)]`
@@ -46,7 +58,7 @@ def score_pairs(pairs, idx0=0, **kwargs):
     else:
         slots, runs_per_slot = mats, nb_runs
     ld = max(m.shape[0] for m in slots)
-    xy = np.zeros((len(slots), ld, 2), np.float32)
+    xy = _staging((len(slots), ld, 2))
     n_rows = np.empty(len(slots), np.int32)
     for k, m in enumerate(slots):
         xy[k, :m.shape[0]] = m

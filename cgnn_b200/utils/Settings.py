@@ -17,7 +17,7 @@ _REFERENCE_DEFAULTS = (
     ("h_layer_dim", 20), ("train_epochs", 1000), ("test_epochs", 500),
     ("use_Fast_MMD", False), ("nb_vectors_approx_MMD", 100), ("complexity_graph_param", 0.00005),
 )
-_ENGINE_DEFAULTS = (("seed", 0), ("exp_policy", 1), ("verbose", True))
+_ENGINE_DEFAULTS = (("seed", 0), ("exp_policy", 3), ("verbose", True))
 
 
 class EngineSettings(object):

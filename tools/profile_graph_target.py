@@ -1,0 +1,20 @@
+"""Small fixed workload for ncu: one launch of the graph instance kernel on the bundled 22-variable
+example (148 instances = one wave).  Usage: python tools/profile_graph_target.py [pol] [train] [test]"""
+import os, sys
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import numpy as np, pandas as pd
+from cgnn_b200 import Engine, DirectedGraph
+from cgnn_b200.plan import build_plan
+from cgnn_b200.utils.scaling import scale
+pol = int(sys.argv[1]) if len(sys.argv) > 1 else 3
+train = int(sys.argv[2]) if len(sys.argv) > 2 else 8
+test = int(sys.argv[3]) if len(sys.argv) > 3 else 4
+EX = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "examples")
+data = pd.read_csv(os.path.join(EX, "Example_graph_numdata.csv"))
+dag = DirectedGraph(pd.read_csv(os.path.join(EX, "Example_graph_target.csv")))
+plan = build_plan(dag, columns=list(data.columns))
+X = scale(data.values).astype(np.float32)
+eng = Engine(0)
+for rep in range(2):
+    r = eng.run_graph(X, [plan] * 4, n_runs=37, h_layer_dim=20, train_epochs=train, test_epochs=test, exp_policy=pol, seed=1)
+    print("graph pol %d: 148 instances x (%d+%d) steps: kernel %.3f ms, mean score %.4f" % (pol, train, test, eng.last_kernel_ms, float(np.mean(r["scores"]))))
