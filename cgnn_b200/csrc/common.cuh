@@ -169,6 +169,39 @@ __device__ __forceinline__ float4 normal4(uint4 r) {
 enum : uint32_t { STREAM_NOISE = 0u, STREAM_INIT = 1u };
 
 // ---------------------------------------------------------------------------------------------
+// Packed FP32x2 arithmetic (Blackwell FFMA2 / FADD2 / FMUL2): one issue slot for two IEEE fp32
+// operations on a register pair.  Same rounding as the scalar instructions; used where the kernels
+// are issue-bound and the data already sits in adjacent registers (float4 column loads).
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ unsigned long long pk(float2 a) {
+    unsigned long long r;
+    asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(a.x), "f"(a.y));
+    return r;
+}
+__device__ __forceinline__ float2 upk(unsigned long long r) {
+    float2 a;
+    asm("mov.b64 {%0, %1}, %2;" : "=f"(a.x), "=f"(a.y) : "l"(r));
+    return a;
+}
+__device__ __forceinline__ float2 ffma2(float2 a, float2 b, float2 c) {
+    unsigned long long d;
+    asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(pk(a)), "l"(pk(b)), "l"(pk(c)));
+    return upk(d);
+}
+__device__ __forceinline__ float2 fadd2(float2 a, float2 b) {
+    unsigned long long d;
+    asm("add.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(pk(a)), "l"(pk(b)));
+    return upk(d);
+}
+__device__ __forceinline__ float2 fsub2(float2 a, float2 b) { return fadd2(a, make_float2(-b.x, -b.y)); }
+__device__ __forceinline__ float2 fmul2(float2 a, float2 b) {
+    unsigned long long d;
+    asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(pk(a)), "l"(pk(b)));
+    return upk(d);
+}
+__device__ __forceinline__ float2 splat2(float w) { return make_float2(w, w); }
+
+// ---------------------------------------------------------------------------------------------
 // Order-independent accumulation into shared memory: 64-bit fixed point (2^-36 resolution,
 // +-2^27 range) with native integer atomics.  Integer addition is associative, so the result does
 // not depend on warp scheduling: the engine is bit-reproducible run to run.

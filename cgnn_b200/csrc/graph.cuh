@@ -32,12 +32,27 @@ constexpr int GR_MAX_H = 32;
 constexpr int GR_MAX_IN = 384;           // sum over nodes of (parents + noise inputs)
 constexpr uint32_t GR_STREAM_NOISE0 = 2u;
 
+// Parameters live in shared memory in a PADDED layout: every hidden vector (a row of W_in, b_in, W_out)
+// occupies HP floats (HP = 20 or 32 >= h, compile-time), the tail being zero for ever (its gradient is
+// exactly 0), so the generator loops are fully unrolled 128-bit / FFMA2 code without tail predicates.
+// Node k: [W_in (n_in x HP) | b_in (HP) | W_out (HP) | b_out, 3 pad] at pad_off[k]; the caller-visible flat
+// layout [W_in (n_in x h) | b_in (h) | W_out (h) | b_out] starts at par_off[k].
 struct GraphDesc {
-    int n_var, n_noise, n_params, n_in_total;
+    int n_var, n_noise, n_params, n_in_total, n_params_pad, pad0, pad1, pad2;
     short col[GR_MAX_VAR], n_par[GR_MAX_VAR], n_in[GR_MAX_VAR];
-    int in_off[GR_MAX_VAR], par_off[GR_MAX_VAR];
+    int in_off[GR_MAX_VAR], par_off[GR_MAX_VAR], pad_off[GR_MAX_VAR];
     short in_idx[GR_MAX_IN];
 };
+
+// caller-visible parameter index -> index in the padded shared-memory layout
+__device__ __forceinline__ int gr_pad_index(const GraphDesc& g, int q, int h, int HP) {
+    int k = 0;
+    while (k + 1 < g.n_var && g.par_off[k + 1] <= q) ++k;
+    const int local = q - g.par_off[k], n_in = g.n_in[k];
+    const int row = local / h, kk = local - row * h;           // rows 0..n_in-1: W_in, n_in: b_in, n_in+1: W_out
+    if (row >= n_in + 2) return g.pad_off[k] + (n_in + 2) * HP;   // b_out
+    return g.pad_off[k] + row * HP + kk;
+}
 
 struct GraphArgs {
     const float* T;            // [n_T][NP][DP]
@@ -93,38 +108,45 @@ __device__ __forceinline__ void gr_fill_noise(const GrSmem& s, const GraphArgs& 
     __syncwarp();
 }
 
-// hidden pre-activations of node k for this lane's row: z[kk] = b_in[kk] + sum_p u_p W_in[p][kk]
-template <int DP>
-__device__ __forceinline__ void gr_node_z(const GrSmem& s, const float* nb, int k, int i, int lane, int h, float (&z)[GR_MAX_H]) {
+// hidden pre-activations of node k for this lane's row: z[kk] = b_in[kk] + sum_p u_p W_in[p][kk], as HP/2 pairs
+template <int DP, int HP>
+__device__ __forceinline__ void gr_node_z(const GrSmem& s, const float* nb, int k, int i, int lane, float2 (&z)[HP / 2]) {
     const GraphDesc& g = *s.desc;
-    const float* th = s.theta + g.par_off[k];
+    const float* th = s.theta + g.pad_off[k];
     const int n_in = g.n_in[k], n_par = g.n_par[k];
     const short* idx = g.in_idx + g.in_off[k];
-    const float* b_in = th + n_in * h;
+    const float4* b4 = reinterpret_cast<const float4*>(th + n_in * HP);
 #pragma unroll
-    for (int kk = 0; kk < GR_MAX_H; ++kk) z[kk] = (kk < h) ? b_in[kk] : 0.f;
+    for (int q = 0; q < HP / 4; ++q) { const float4 b = b4[q]; z[2 * q] = make_float2(b.x, b.y); z[2 * q + 1] = make_float2(b.z, b.w); }
     for (int p = 0; p < n_in; ++p) {
-        const float u = (p < n_par) ? s.Pm[i * DP + idx[p]] : nb[idx[p] * 32 + lane];
-        const float* w = th + p * h;
+        const float2 u = splat2((p < n_par) ? s.Pm[i * DP + idx[p]] : nb[idx[p] * 32 + lane]);
+        const float4* w4 = reinterpret_cast<const float4*>(th + p * HP);
 #pragma unroll
-        for (int kk = 0; kk < GR_MAX_H; ++kk)
-            if (kk < h) z[kk] = fmaf(u, w[kk], z[kk]);
+        for (int q = 0; q < HP / 4; ++q) {
+            const float4 w = w4[q];
+            z[2 * q] = ffma2(u, make_float2(w.x, w.y), z[2 * q]);
+            z[2 * q + 1] = ffma2(u, make_float2(w.z, w.w), z[2 * q + 1]);
+        }
     }
 }
 
 // Generator forward of one row block (CGNN.py:63-84), nodes in build order.
-template <int DP>
-__device__ __forceinline__ void gr_forward_block(const GrSmem& s, const float* nb, int i, int lane, int h) {
+template <int DP, int HP>
+__device__ __forceinline__ void gr_forward_block(const GrSmem& s, const float* nb, int i, int lane) {
     const GraphDesc& g = *s.desc;
     for (int k = 0; k < g.n_var; ++k) {
-        float z[GR_MAX_H];
-        gr_node_z<DP>(s, nb, k, i, lane, h, z);
-        const float* w_out = s.theta + g.par_off[k] + g.n_in[k] * h + h;
-        float out = w_out[h];
+        float2 z[HP / 2];
+        gr_node_z<DP, HP>(s, nb, k, i, lane, z);
+        const float* w_out = s.theta + g.pad_off[k] + (g.n_in[k] + 1) * HP;
+        const float4* w4 = reinterpret_cast<const float4*>(w_out);
+        float2 acc = make_float2(w_out[HP], 0.f);                       // b_out
 #pragma unroll
-        for (int kk = 0; kk < GR_MAX_H; ++kk)
-            if (kk < h) out = fmaf(fmaxf(z[kk], 0.f), w_out[kk], out);
-        s.Pm[i * DP + g.col[k]] = out;
+        for (int q = 0; q < HP / 4; ++q) {
+            const float4 w = w4[q];
+            acc = ffma2(make_float2(fmaxf(z[2 * q].x, 0.f), fmaxf(z[2 * q].y, 0.f)), make_float2(w.x, w.y), acc);
+            acc = ffma2(make_float2(fmaxf(z[2 * q + 1].x, 0.f), fmaxf(z[2 * q + 1].y, 0.f)), make_float2(w.z, w.w), acc);
+        }
+        s.Pm[i * DP + g.col[k]] = acc.x + acc.y;
     }
 }
 
@@ -141,49 +163,56 @@ __device__ __forceinline__ void gr_load_col_gmem(const float* __restrict__ base,
     for (int q = 0; q < DP / 4; ++q) { const float4 v = __ldg(r + q); t[4 * q] = v.x; t[4 * q + 1] = v.y; t[4 * q + 2] = v.z; t[4 * q + 3] = v.w; }
 }
 
+// squared distance of this row to column t (DP floats as DP/2 pairs) - four partial sums, packed
+template <int DP>
+__device__ __forceinline__ float gr_sqdist(const float2 (&p)[DP / 2], const float (&t)[DP], float2 (&df)[DP / 2]) {
+    float2 Da = make_float2(0.f, 0.f), Db = make_float2(0.f, 0.f);
+#pragma unroll
+    for (int q = 0; q < DP / 2; ++q) {
+        df[q] = fsub2(p[q], make_float2(t[2 * q], t[2 * q + 1]));
+        if (q & 1) Db = ffma2(df[q], df[q], Db); else Da = ffma2(df[q], df[q], Da);
+    }
+    const float2 D = fadd2(Da, Db);
+    return D.x + D.y;
+}
+
 // MMD gradient of one row: tot[c] = sum_j w(P_i,T_j)(P_ic - T_jc) - sum_j w(P_i,P_j)(P_ic - P_jc)   (unscaled)
 // fp32 accumulation in runs of one PT tile + one PP tile (64 evaluations), then a second-level fp32 sum
-// of the (mutually cancelling, hence small) tile pairs.
+// of the (mutually cancelling, hence small) tile pairs.  All column-wise arithmetic is FFMA2/FADD2.
 template <int DP, int POL>
 __device__ __forceinline__ void gr_mmd_train_row(const float* __restrict__ Pm, const float* __restrict__ T, int N,
-                                                 const float (&p)[DP], float (&tot)[DP]) {
+                                                 const float2 (&p)[DP / 2], float2 (&tot)[DP / 2]) {
 #pragma unroll
-    for (int c = 0; c < DP; ++c) tot[c] = 0.f;
+    for (int q = 0; q < DP / 2; ++q) tot[q] = make_float2(0.f, 0.f);
     for (int j0 = 0; j0 < N; j0 += 32) {
         const int j1 = min(j0 + 32, N);
-        float acc[DP];
+        float2 acc[DP / 2];
 #pragma unroll
-        for (int c = 0; c < DP; ++c) acc[c] = 0.f;
-#pragma unroll 2
+        for (int q = 0; q < DP / 2; ++q) acc[q] = make_float2(0.f, 0.f);
         for (int j = j0; j < j1; ++j) {
-            float t[DP], df[DP];
+            float t[DP];
+            float2 df[DP / 2];
             gr_load_col_gmem<DP>(T, j, t);
-            float D = 0.f;
+            const float2 w = splat2(wsum<POL>(gr_sqdist<DP>(p, t, df)));
 #pragma unroll
-            for (int c = 0; c < DP; ++c) { df[c] = p[c] - t[c]; D = fmaf(df[c], df[c], D); }
-            const float w = wsum<POL>(D);
-#pragma unroll
-            for (int c = 0; c < DP; ++c) acc[c] = fmaf(w, df[c], acc[c]);
+            for (int q = 0; q < DP / 2; ++q) acc[q] = ffma2(w, df[q], acc[q]);
         }
-#pragma unroll 2
         for (int j = j0; j < j1; ++j) {
-            float t[DP], df[DP];
+            float t[DP];
+            float2 df[DP / 2];
             gr_load_col_smem<DP>(Pm, j, t);
-            float D = 0.f;
+            const float2 w = splat2(-wsum<POL>(gr_sqdist<DP>(p, t, df)));
 #pragma unroll
-            for (int c = 0; c < DP; ++c) { df[c] = p[c] - t[c]; D = fmaf(df[c], df[c], D); }
-            const float w = -wsum<POL>(D);
-#pragma unroll
-            for (int c = 0; c < DP; ++c) acc[c] = fmaf(w, df[c], acc[c]);
+            for (int q = 0; q < DP / 2; ++q) acc[q] = ffma2(w, df[q], acc[q]);
         }
 #pragma unroll
-        for (int c = 0; c < DP; ++c) tot[c] += acc[c];
+        for (int q = 0; q < DP / 2; ++q) tot[q] = fadd2(tot[q], acc[q]);
     }
 }
 
 // Loss share of one row: sum_j [ k(R_i, B_j) ] over a column source (smem or gmem), fp64 across tiles.
 template <int DP, int POL, bool GMEM>
-__device__ __forceinline__ double gr_mmd_eval_row(const float* __restrict__ B, int N, const float (&p)[DP]) {
+__device__ __forceinline__ double gr_mmd_eval_row(const float* __restrict__ B, int N, const float2 (&p)[DP / 2]) {
     double tot = 0.0;
     for (int j0 = 0; j0 < N; j0 += 64) {
         const int j1 = min(j0 + 64, N);
@@ -191,59 +220,74 @@ __device__ __forceinline__ double gr_mmd_eval_row(const float* __restrict__ B, i
 #pragma unroll 2
         for (int j = j0; j < j1; ++j) {
             float t[DP];
+            float2 df[DP / 2];
             if (GMEM) gr_load_col_gmem<DP>(B, j, t); else gr_load_col_smem<DP>(B, j, t);
-            float D = 0.f;
-#pragma unroll
-            for (int c = 0; c < DP; ++c) { const float df = p[c] - t[c]; D = fmaf(df, df, D); }
-            acc += ksum<POL>(D);
+            acc += ksum<POL>(gr_sqdist<DP>(p, t, df));
         }
         tot += double(acc);
     }
     return tot;
 }
 
+// element kk of a hidden vector held as HP/2 register pairs (kk is a compile-time constant after unrolling)
+template <int HP>
+__device__ __forceinline__ float gr_zget(const float2 (&z)[HP / 2], int kk) {
+    return (kk & 1) ? z[(kk >> 1) % (HP / 2)].y : z[(kk >> 1) % (HP / 2)].x;
+}
+
 // Thread-local backward of one row through all nodes in reverse build order; parameter gradients are
 // reduced over the 32 rows of the block (warp_reduce32) and added to the shared fixed-point accumulators.
-template <int DP>
-__device__ __forceinline__ void gr_backward_block(const GrSmem& s, const float* nb, int i, int lane, int h, float* gl) {
+template <int DP, int HP>
+__device__ __forceinline__ void gr_backward_block(const GrSmem& s, const float* nb, int i, int lane, float* gl) {
     const GraphDesc& g = *s.desc;
     for (int k = g.n_var - 1; k >= 0; --k) {
-        float z[GR_MAX_H], v[32];
-        gr_node_z<DP>(s, nb, k, i, lane, h, z);
+        float2 z[HP / 2];
+        float v[32];
+        gr_node_z<DP, HP>(s, nb, k, i, lane, z);
         const int n_in = g.n_in[k], n_par = g.n_par[k];
-        const int off = g.par_off[k];
+        const int off = g.pad_off[k];
         const short* idx = g.in_idx + g.in_off[k];
-        const float* w_out = s.theta + off + n_in * h + h;
+        const float* w_out = s.theta + off + (n_in + 1) * HP;
         const float delta = gl[g.col[k]];
         // b_out
         const float sb = warp_sum(delta);
-        if (lane == 0) fx_add(&s.g64[off + n_in * h + 2 * h], double(sb));
+        if (lane == 0) fx_add(&s.g64[off + (n_in + 2) * HP], double(sb));
         // W_out, then dz in place of z
 #pragma unroll
-        for (int kk = 0; kk < 32; ++kk) v[kk] = (kk < h) ? fmaxf(z[kk], 0.f) * delta : 0.f;
+        for (int kk = 0; kk < 32; ++kk) {
+            v[kk] = (kk < HP) ? fmaxf(gr_zget<HP>(z, kk), 0.f) * delta : 0.f;
+        }
         float r = warp_reduce32(v, lane);
-        if (lane < h) fx_add(&s.g64[off + n_in * h + h + lane], double(r));
+        if (lane < HP) fx_add(&s.g64[off + (n_in + 1) * HP + lane], double(r));
 #pragma unroll
-        for (int kk = 0; kk < GR_MAX_H; ++kk) z[kk] = (kk < h && z[kk] > 0.f) ? delta * w_out[kk] : 0.f;
+        for (int q = 0; q < HP / 2; ++q) {
+            z[q].x = z[q].x > 0.f ? delta * w_out[2 * q] : 0.f;
+            z[q].y = z[q].y > 0.f ? delta * w_out[2 * q + 1] : 0.f;
+        }
         // b_in
 #pragma unroll
-        for (int kk = 0; kk < 32; ++kk) v[kk] = z[kk];
+        for (int kk = 0; kk < 32; ++kk)
+            v[kk] = (kk < HP) ? (gr_zget<HP>(z, kk)) : 0.f;
         r = warp_reduce32(v, lane);
-        if (lane < h) fx_add(&s.g64[off + n_in * h + lane], double(r));
+        if (lane < HP) fx_add(&s.g64[off + n_in * HP + lane], double(r));
         // W_in rows and input gradients
         for (int p = 0; p < n_in; ++p) {
             const float u = (p < n_par) ? s.Pm[i * DP + idx[p]] : nb[idx[p] * 32 + lane];
 #pragma unroll
-            for (int kk = 0; kk < 32; ++kk) v[kk] = u * z[kk];
+            for (int kk = 0; kk < 32; ++kk)
+                v[kk] = (kk < HP) ? u * (gr_zget<HP>(z, kk)) : 0.f;
             r = warp_reduce32(v, lane);
-            if (lane < h) fx_add(&s.g64[off + p * h + lane], double(r));
+            if (lane < HP) fx_add(&s.g64[off + p * HP + lane], double(r));
             if (p < n_par) {
-                const float* w = s.theta + off + p * h;
-                float du = 0.f;
+                const float4* w4 = reinterpret_cast<const float4*>(s.theta + off + p * HP);
+                float2 du = make_float2(0.f, 0.f);
 #pragma unroll
-                for (int kk = 0; kk < GR_MAX_H; ++kk)
-                    if (kk < h) du = fmaf(z[kk], w[kk], du);
-                gl[idx[p]] += du;
+                for (int q = 0; q < HP / 4; ++q) {
+                    const float4 w = w4[q];
+                    du = ffma2(z[2 * q], make_float2(w.x, w.y), du);
+                    du = ffma2(z[2 * q + 1], make_float2(w.z, w.w), du);
+                }
+                gl[idx[p]] += du.x + du.y;
             }
         }
     }
@@ -261,7 +305,7 @@ __device__ __forceinline__ double gr_block_sum(double v, double* red, int warp, 
     return t;
 }
 
-template <int DP, int POL>
+template <int DP, int HP, int POL>
 __global__ void __launch_bounds__(GR_NT, 1) graph_kernel(const GraphArgs a) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     __shared__ int s_inst;
@@ -308,18 +352,18 @@ __global__ void __launch_bounds__(GR_NT, 1) graph_kernel(const GraphArgs a) {
         }
         for (int q = tid; q < a.NP * DP; q += GR_NT) s.Pm[q] = 0.f;
         __syncthreads();
-        const int P = s.desc->n_params;
-        for (int q = tid; q < pp; q += GR_NT) {
-            float th = 0.f;
-            if (q < P) {
-                if (a.init_params) th = a.init_params[size_t(out) * a.ld_params + q];
-                else {
-                    const float4 n = normal4(philox4x32_10(make_uint4(q >> 2, 0u, STREAM_INIT, uid), key));
-                    const int e = q & 3;
-                    th = a.init_std * (e == 0 ? n.x : e == 1 ? n.y : e == 2 ? n.z : n.w);
-                }
+        const int P = s.desc->n_params, PPAD = s.desc->n_params_pad;
+        for (int q = tid; q < pp; q += GR_NT) { s.theta[q] = 0.f; s.am[q] = 0.f; s.av[q] = 0.f; s.g64[q] = 0; }
+        __syncthreads();
+        for (int q = tid; q < P; q += GR_NT) {
+            float th;
+            if (a.init_params) th = a.init_params[size_t(out) * a.ld_params + q];
+            else {
+                const float4 n = normal4(philox4x32_10(make_uint4(q >> 2, 0u, STREAM_INIT, uid), key));
+                const int e = q & 3;
+                th = a.init_std * (e == 0 ? n.x : e == 1 ? n.y : e == 2 ? n.z : n.w);
             }
-            s.theta[q] = th; s.am[q] = 0.f; s.av[q] = 0.f; s.g64[q] = 0;
+            s.theta[gr_pad_index(*s.desc, q, h, HP)] = th;
         }
         if (tid == 0) { s.red[GR_NW + 1] = 1.0; s.red[GR_NW + 2] = 1.0; }
         // ---- TT (constant per instance) -------------------------------------------------------
@@ -327,8 +371,11 @@ __global__ void __launch_bounds__(GR_NT, 1) graph_kernel(const GraphArgs a) {
             double part = 0.0;
             for (int rb = warp; rb < NB; rb += GR_NW) {
                 const int i = 32 * rb + lane;
-                float p[DP];
-                gr_load_col_gmem<DP>(T, min(i, N - 1), p);
+                float pf[DP];
+                float2 p[DP / 2];
+                gr_load_col_gmem<DP>(T, min(i, N - 1), pf);
+#pragma unroll
+                for (int q = 0; q < DP / 2; ++q) p[q] = make_float2(pf[2 * q], pf[2 * q + 1]);
                 const double v = gr_mmd_eval_row<DP, POL, true>(T, N, p);
                 if (i < N) part += v;
             }
@@ -350,7 +397,7 @@ __global__ void __launch_bounds__(GR_NT, 1) graph_kernel(const GraphArgs a) {
             for (int rb = warp; rb < NB; rb += GR_NW) {
                 const int i = 32 * rb + lane;
                 gr_fill_noise(s, a, nb, i, lane, it, uid, key, noise_step);
-                gr_forward_block<DP>(s, nb, i, lane, h);
+                gr_forward_block<DP, HP>(s, nb, i, lane);
                 __syncwarp();
             }
             __syncthreads();
@@ -365,8 +412,11 @@ __global__ void __launch_bounds__(GR_NT, 1) graph_kernel(const GraphArgs a) {
                 double part = 0.0;
                 for (int rb = warp; rb < NB; rb += GR_NW) {
                     const int i = 32 * rb + lane;
-                    float p[DP];
-                    gr_load_col_smem<DP>(s.Pm, i, p);
+                    float pf[DP];
+                    float2 p[DP / 2];
+                    gr_load_col_smem<DP>(s.Pm, i, pf);
+#pragma unroll
+                    for (int q = 0; q < DP / 2; ++q) p[q] = make_float2(pf[2 * q], pf[2 * q + 1]);
                     const double v = gr_mmd_eval_row<DP, POL, false>(s.Pm, N, p) - 2.0 * gr_mmd_eval_row<DP, POL, true>(T, N, p);
                     if (i < N) part += v;
                 }
@@ -386,35 +436,48 @@ __global__ void __launch_bounds__(GR_NT, 1) graph_kernel(const GraphArgs a) {
                 const int i = 32 * rb + lane;
                 float gl[DP];
                 {
-                    float p[DP], tot[DP];
-                    gr_load_col_smem<DP>(s.Pm, i, p);
+                    float pf[DP];
+                    float2 p[DP / 2], tot[DP / 2];
+                    gr_load_col_smem<DP>(s.Pm, i, pf);
+#pragma unroll
+                    for (int q = 0; q < DP / 2; ++q) p[q] = make_float2(pf[2 * q], pf[2 * q + 1]);
                     gr_mmd_train_row<DP, POL>(s.Pm, T, N, p, tot);
 #pragma unroll
-                    for (int c = 0; c < DP; ++c) gl[c] = (i < N) ? tot[c] * scale : 0.f;
+                    for (int q = 0; q < DP / 2; ++q) {
+                        gl[2 * q] = (i < N) ? tot[q].x * scale : 0.f;
+                        gl[2 * q + 1] = (i < N) ? tot[q].y * scale : 0.f;
+                    }
                 }
                 if (a.dbg_dldp && i < N)
                     for (int c = 0; c < s.desc->n_var; ++c) a.dbg_dldp[(size_t(it) * N + i) * s.desc->n_var + c] = gl[c];
                 gr_fill_noise(s, a, nb, i, lane, it, uid, key, noise_step);
-                gr_backward_block<DP>(s, nb, i, lane, h, gl);
+                gr_backward_block<DP, HP>(s, nb, i, lane, gl);
                 __syncwarp();
             }
             __syncthreads();
             // ---- Adam --------------------------------------------------------------------------
             {
                 const float lr_t = float(s.red[GR_NW + 3]);
-                for (int q = tid; q < P; q += GR_NT) {
+                if (a.dbg_grad)
+                    for (int q = tid; q < P; q += GR_NT)
+                        a.dbg_grad[size_t(it) * P + q] = float(fx_get(&s.g64[gr_pad_index(*s.desc, q, h, HP)]));
+                if (a.dbg_grad) __syncthreads();
+                for (int q = tid; q < PPAD; q += GR_NT) {      // pad entries: gradient 0, moments 0 -> they stay 0
                     const float g = float(fx_get(&s.g64[q]));
                     s.g64[q] = 0;
                     float m = s.am[q], v = s.av[q];
                     const float th = adam_update(s.theta[q], g, m, v, lr_t);
                     s.am[q] = m; s.av[q] = v; s.theta[q] = th;
-                    if (a.dbg_grad) a.dbg_grad[size_t(it) * P + q] = g;
-                    if (a.dbg_params) a.dbg_params[size_t(it) * P + q] = th;
+                }
+                if (a.dbg_params) {
+                    __syncthreads();
+                    for (int q = tid; q < P; q += GR_NT) a.dbg_params[size_t(it) * P + q] = s.theta[gr_pad_index(*s.desc, q, h, HP)];
                 }
             }
             if (it == a.train_epochs - 1 && a.params_out) {
                 __syncthreads();
-                for (int q = tid; q < P; q += GR_NT) a.params_out[size_t(out) * a.ld_params + q] = s.theta[q];
+                for (int q = tid; q < P; q += GR_NT)
+                    a.params_out[size_t(out) * a.ld_params + q] = s.theta[gr_pad_index(*s.desc, q, h, HP)];
             }
         }
         if (tid == 0 && a.scores) a.scores[out] = a.test_epochs > 0 ? float(score_sum / double(a.test_epochs)) : 0.f;

@@ -21,7 +21,9 @@ static __global__ void gather_rows_kernel(const float* __restrict__ data, int n_
 }
 
 
-#define DECL(DP_) cudaError_t cgnn_launch_graph_dp##DP_(int, const GraphArgs&, int, size_t, cudaStream_t);
+#define DECL(DP_)                                                                                  \
+    cudaError_t cgnn_launch_graph_dp##DP_##_hp20(int, const GraphArgs&, int, size_t, cudaStream_t); \
+    cudaError_t cgnn_launch_graph_dp##DP_##_hp32(int, const GraphArgs&, int, size_t, cudaStream_t);
 DECL(8) DECL(16) DECL(20) DECL(24) DECL(32)
 #undef DECL
 
@@ -32,14 +34,11 @@ static int pick_dp(int n_var) {
     return 0;
 }
 
-static cudaError_t launch_graph(int dp, int pol, const GraphArgs& a, int grid, size_t smem, cudaStream_t st) {
-    switch (dp) {
-        case 8: return cgnn_launch_graph_dp8(pol, a, grid, smem, st);
-        case 16: return cgnn_launch_graph_dp16(pol, a, grid, smem, st);
-        case 20: return cgnn_launch_graph_dp20(pol, a, grid, smem, st);
-        case 24: return cgnn_launch_graph_dp24(pol, a, grid, smem, st);
-        case 32: return cgnn_launch_graph_dp32(pol, a, grid, smem, st);
-    }
+static cudaError_t launch_graph(int dp, int hp, int pol, const GraphArgs& a, int grid, size_t smem, cudaStream_t st) {
+#define CASE(DP_) \
+    case DP_: return hp == 20 ? cgnn_launch_graph_dp##DP_##_hp20(pol, a, grid, smem, st) : cgnn_launch_graph_dp##DP_##_hp32(pol, a, grid, smem, st);
+    switch (dp) { CASE(8) CASE(16) CASE(20) CASE(24) CASE(32) }
+#undef CASE
     return cudaErrorInvalidValue;
 }
 
@@ -69,20 +68,21 @@ static int run_graph_impl(cgnn_ctx* ctx, const cgnn_hparams* hp, const float* da
     CU(cudaSetDevice(ctx->device));
 
     const int h = hp->h_layer_dim;
+    const int HP = h <= 20 ? 20 : 32;                    // padded hidden width of the shared-memory layout
     const int n_graphs = gb->n_graphs;
     const int n_inst = dbg_host ? 1 : n_graphs * n_runs;
     const int epochs = hp->train_epochs + hp->test_epochs;
 
     // ---- descriptors ---------------------------------------------------------------------------
     std::vector<GraphDesc> descs(n_graphs);
-    int p_max = 0;
+    int p_max = 0, p_pad_max = 0;
     for (int g = 0; g < n_graphs; ++g) {
         GraphDesc& d = descs[g];
         std::memset(&d, 0, sizeof d);
         d.n_var = n_var; d.n_noise = n_noise;
         const int base = gb->in_ptr[g], end = gb->in_ptr[g + 1];
         if (end - base > GR_MAX_IN) return fail(ctx, CGNN_ERR_LIMIT, "graph %d has %d inputs in total (limit %d)", g, end - base, GR_MAX_IN);
-        int io = 0, po = 0;
+        int io = 0, po = 0, ppad = 0;
         unsigned int seen = 0;
         for (int k = 0; k < n_var; ++k) {
             const int col = gb->node_col[g * n_var + k], npar = gb->n_parents[g * n_var + k], nin = gb->n_inputs[g * n_var + k];
@@ -100,13 +100,15 @@ static int run_graph_impl(cgnn_ctx* ctx, const cgnn_hparams* hp, const float* da
             }
             seen |= 1u << col;
             d.col[k] = short(col); d.n_par[k] = short(npar); d.n_in[k] = short(nin);
-            d.in_off[k] = io; d.par_off[k] = po;
+            d.in_off[k] = io; d.par_off[k] = po; d.pad_off[k] = ppad;
             io += nin;
             po += nin * h + 2 * h + 1;
+            ppad += (nin + 2) * HP + 4;
         }
         if (base + io != end) return fail(ctx, CGNN_ERR_ARG, "graph %d: in_ptr does not match the sum of n_inputs", g);
-        d.n_in_total = io; d.n_params = po;
+        d.n_in_total = io; d.n_params = po; d.n_params_pad = ppad;
         p_max = std::max(p_max, po);
+        p_pad_max = std::max(p_pad_max, ppad);
     }
     if ((init_params || params_out) && ld_params < p_max)
         return fail(ctx, CGNN_ERR_ARG, "ld_params=%d smaller than the largest parameter count %d", ld_params, p_max);
@@ -195,19 +197,19 @@ static int run_graph_impl(cgnn_ctx* ctx, const cgnn_hparams* hp, const float* da
         a.dbg_loss = dbg_dev[0]; a.dbg_pred = dbg_dev[1]; a.dbg_dldp = dbg_dev[2]; a.dbg_grad = dbg_dev[3]; a.dbg_params = dbg_dev[4];
     }
 
-    a.n_inst = n_inst; a.N = n_rows; a.NP = NP; a.n_noise = n_noise; a.p_max = p_max;
+    a.n_inst = n_inst; a.N = n_rows; a.NP = NP; a.n_noise = n_noise; a.p_max = p_pad_max;
     a.h = h; a.train_epochs = hp->train_epochs; a.test_epochs = hp->test_epochs; a.trace_every = hp->trace_every;
     a.lr = hp->learning_rate; a.init_std = hp->init_std; a.ld_params = ld_params;
     a.key = make_uint2((unsigned int)(hp->seed & 0xffffffffu), (unsigned int)(hp->seed >> 32));
 
-    const size_t smem = gr_smem_bytes(NP, DP, n_noise, p_max);
+    const size_t smem = gr_smem_bytes(NP, DP, n_noise, p_pad_max);
     if (smem > size_t(ctx->prop.sharedMemPerBlockOptin))
         return fail(ctx, CGNN_ERR_LIMIT, "graph instance needs %zu B of shared memory (rows %d x cols %d, %d noise columns, %d parameters); "
                     "device allows %zu", smem, n_rows, DP, n_noise, p_max, size_t(ctx->prop.sharedMemPerBlockOptin));
     const int grid = std::min(n_inst, ctx->prop.multiProcessorCount);
 
     CU(cudaEventRecord(ctx->ev0, ctx->stream));
-    cudaError_t le = launch_graph(DP, hp->exp_policy, a, grid, smem, ctx->stream);
+    cudaError_t le = launch_graph(DP, HP, hp->exp_policy, a, grid, smem, ctx->stream);
     if (le != cudaSuccess) return fail(ctx, CGNN_ERR_CUDA, "graph kernel launch: %s", cudaGetErrorString(le));
     CU(cudaEventRecord(ctx->ev1, ctx->stream));
     ctx->last_launches = 2;
