@@ -202,6 +202,57 @@ __device__ __forceinline__ float2 fmul2(float2 a, float2 b) {
 __device__ __forceinline__ float2 splat2(float w) { return make_float2(w, w); }
 
 // ---------------------------------------------------------------------------------------------
+// Two evaluations at once: the chains of wsum_p / ksum_p on register pairs (FMUL2 / FFMA2), the MUFU
+// ex2 on each half.  Halves the issue slots of the FP32 part, which is what bounds exp policy 3.
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ float2 ex2f2(float2 x) { return make_float2(ex2f(x.x), ex2f(x.y)); }
+
+template <int POL>
+__device__ __forceinline__ float2 wsum_p2(float2 Dp) {
+    const float2 q = ex2f2(fmul2(Dp, splat2(-0.02f)));
+    const float2 p = ex2f2(make_float2(-Dp.x, -Dp.y));
+    float2 w = ex2f2(ffma2(Dp, splat2(-200.0f), splat2(CGNN_LOG2_50)));
+    if (POL >= 2) {
+        const float2 q2 = fmul2(q, q), q4 = fmul2(q2, q2), q8 = fmul2(q4, q4);
+        w = ffma2(ffma2(splat2(G1), fmul2(q8, q), splat2(G0)), q, w);
+    } else {
+        w = ffma2(splat2(G1), ex2f2(fmul2(Dp, splat2(-0.2f))), ffma2(splat2(G0), q, w));
+    }
+    if (POL >= 1) {
+        const float2 p2 = fmul2(p, p);
+        w = ffma2(ffma2(fadd2(p2, splat2(G3)), p, splat2(G2)), p, w);
+        if (POL >= 3) { const float2 p4 = fmul2(p2, p2), p8 = fmul2(p4, p4); w = ffma2(splat2(G5), fmul2(fmul2(p8, p8), p4), w); }
+        else w = ffma2(splat2(G5), ex2f2(fmul2(Dp, splat2(-20.0f))), w);
+    } else {
+        w = ffma2(splat2(G2), p, w);
+        w = ffma2(splat2(G3), ex2f2(fmul2(Dp, splat2(-2.0f))), w);
+        w = fadd2(w, ex2f2(fmul2(Dp, splat2(-4.0f))));
+        w = ffma2(splat2(G5), ex2f2(fmul2(Dp, splat2(-20.0f))), w);
+    }
+    return w;
+}
+
+template <int POL>
+__device__ __forceinline__ float2 ksum_p2(float2 Dp) {
+    const float2 q = ex2f2(fmul2(Dp, splat2(-0.02f)));
+    const float2 p = ex2f2(make_float2(-Dp.x, -Dp.y));
+    float2 s = ex2f2(fmul2(Dp, splat2(-200.0f)));
+    if (POL >= 2) { const float2 q2 = fmul2(q, q), q4 = fmul2(q2, q2), q5 = fmul2(q4, q); s = fadd2(s, ffma2(q5, q5, q)); }
+    else s = fadd2(s, fadd2(q, ex2f2(fmul2(Dp, splat2(-0.2f)))));
+    if (POL >= 1) {
+        const float2 p2 = fmul2(p, p), p4 = fmul2(p2, p2);
+        float2 t = fadd2(ffma2(p2, p2, p2), p);
+        if (POL >= 3) { const float2 p8 = fmul2(p4, p4); t = ffma2(fmul2(p8, p8), p4, t); }
+        else t = fadd2(t, ex2f2(fmul2(Dp, splat2(-20.0f))));
+        s = fadd2(s, t);
+    } else {
+        s = fadd2(s, fadd2(fadd2(p, ex2f2(fmul2(Dp, splat2(-2.0f)))),
+                           fadd2(ex2f2(fmul2(Dp, splat2(-4.0f))), ex2f2(fmul2(Dp, splat2(-20.0f))))));
+    }
+    return s;
+}
+
+// ---------------------------------------------------------------------------------------------
 // Order-independent accumulation into shared memory: 64-bit fixed point (2^-36 resolution,
 // +-2^27 range) with native integer atomics.  Integer addition is associative, so the result does
 // not depend on warp scheduling: the engine is bit-reproducible run to run.

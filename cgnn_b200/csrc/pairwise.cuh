@@ -94,62 +94,67 @@ __device__ __forceinline__ int pw_npp(int I, int NB) {
 }
 
 // Off-diagonal tile pair, gradient form.  tile = &Qd[64 J + lane].  Returns the row-side sum for row i;
-// colsum receives the total for column 32 J + lane (both in primed units, unscaled).
+// colsum receives the total for column 32 J + lane (both in primed units, unscaled).  Two steps of the
+// walk are evaluated together: their six kernel evaluations run as three FP32x2-packed chains.
 template <int POL>
 __device__ __forceinline__ float trio_train(float xi, float yi, float yhi, const float4* __restrict__ tile, int lane,
                                             float& colsum) {
-    float ra = 0.f, ca = 0.f;
+    float2 ra = make_float2(0.f, 0.f);
+    float ca = 0.f;
     const int src = (lane + 1) & 31;
-#pragma unroll 4
-    for (int s = 0; s < 32; ++s) {
-        const float4 c = tile[s];
-        const float dx = xi - c.x;
-        const float dx2 = dx * dx;
-        const float a = yhi - c.z;      // PP(i,j):  yhat_i - yhat_j
-        const float b = yhi - c.y;      // PT(i,j):  yhat_i - y_j
-        const float d = c.z - yi;       // PT(j,i):  yhat_j - y_i
-        const float wpp = wsum_p<POL>(fmaf(a, a, dx2));
-        const float w1 = wsum_p<POL>(fmaf(b, b, dx2));
-        const float w2 = wsum_p<POL>(fmaf(d, d, dx2));
-        ra = fmaf(w1, b, ra);
-        ra = fmaf(-wpp, a, ra);
-        ca = fmaf(wpp, a, ca);
-        ca = fmaf(w2, d, ca);
-        ca = __shfl_sync(0xffffffffu, ca, src);
+#pragma unroll 2
+    for (int s = 0; s < 32; s += 2) {
+        const float4 c0 = tile[s], c1 = tile[s + 1];
+        const float dx0 = xi - c0.x, dx1 = xi - c1.x;
+        const float e0 = dx0 * dx0, e1 = dx1 * dx1;
+        const float2 a = make_float2(yhi - c0.z, yhi - c1.z);      // PP(i,j):  yhat_i - yhat_j
+        const float2 b = make_float2(yhi - c0.y, yhi - c1.y);      // PT(i,j):  yhat_i - y_j
+        const float2 d = make_float2(c0.z - yi, c1.z - yi);        // PT(j,i):  yhat_j - y_i
+        const float2 wpp = wsum_p2<POL>(make_float2(fmaf(a.x, a.x, e0), fmaf(a.y, a.y, e1)));
+        const float2 w1 = wsum_p2<POL>(make_float2(fmaf(b.x, b.x, e0), fmaf(b.y, b.y, e1)));
+        const float2 w2 = wsum_p2<POL>(make_float2(fmaf(d.x, d.x, e0), fmaf(d.y, d.y, e1)));
+        const float2 wa = fmul2(wpp, a);
+        ra = fsub2(ffma2(w1, b, ra), wa);
+        const float2 cc = ffma2(w2, d, wa);
+        ca = __shfl_sync(0xffffffffu, ca + cc.x, src);
+        ca = __shfl_sync(0xffffffffu, ca + cc.y, src);
     }
     colsum = ca;
-    return ra;
+    return ra.x + ra.y;
 }
 
-// Diagonal tile, gradient form: all ordered pairs of the tile, row side only.
+// Diagonal tile, gradient form: all ordered pairs of the tile, row side only (PT and PP of a step packed).
 template <int POL>
 __device__ __forceinline__ float duo_train(float xi, float yhi, const float4* __restrict__ tile) {
-    float ra = 0.f;
+    float2 ra = make_float2(0.f, 0.f);
 #pragma unroll 4
     for (int s = 0; s < 32; ++s) {
         const float4 c = tile[s];
         const float dx = xi - c.x;
-        const float dx2 = dx * dx;
-        const float a = yhi - c.z, b = yhi - c.y;
-        ra = fmaf(wsum_p<POL>(fmaf(b, b, dx2)), b, ra);
-        ra = fmaf(-wsum_p<POL>(fmaf(a, a, dx2)), a, ra);
+        const float e = dx * dx;
+        const float2 ab = make_float2(yhi - c.y, c.z - yhi);       // (PT: yhat_i - y_j,  PP with the sign folded in)
+        const float2 w = wsum_p2<POL>(make_float2(fmaf(ab.x, ab.x, e), fmaf(ab.y, ab.y, e)));
+        ra = ffma2(w, ab, ra);
     }
-    return ra;
+    return ra.x + ra.y;
 }
 
 // Loss forms: kPP - kPT(i,j) - kPT(j,i) per unordered pair (to be doubled), kPP - 2 kPT per ordered pair.
 template <int POL>
 __device__ __forceinline__ float trio_eval(float xi, float yi, float yhi, const float4* __restrict__ tile) {
-    float acc = 0.f;
-#pragma unroll 4
-    for (int s = 0; s < 32; ++s) {
-        const float4 c = tile[s];
-        const float dx = xi - c.x;
-        const float dx2 = dx * dx;
-        const float a = yhi - c.z, b = yhi - c.y, d = c.z - yi;
-        acc += ksum_p<POL>(fmaf(a, a, dx2)) - (ksum_p<POL>(fmaf(b, b, dx2)) + ksum_p<POL>(fmaf(d, d, dx2)));
+    float2 acc = make_float2(0.f, 0.f);
+#pragma unroll 2
+    for (int s = 0; s < 32; s += 2) {
+        const float4 c0 = tile[s], c1 = tile[s + 1];
+        const float dx0 = xi - c0.x, dx1 = xi - c1.x;
+        const float e0 = dx0 * dx0, e1 = dx1 * dx1;
+        const float a0 = yhi - c0.z, a1 = yhi - c1.z, b0 = yhi - c0.y, b1 = yhi - c1.y, d0 = c0.z - yi, d1 = c1.z - yi;
+        const float2 kpp = ksum_p2<POL>(make_float2(fmaf(a0, a0, e0), fmaf(a1, a1, e1)));
+        const float2 k1 = ksum_p2<POL>(make_float2(fmaf(b0, b0, e0), fmaf(b1, b1, e1)));
+        const float2 k2 = ksum_p2<POL>(make_float2(fmaf(d0, d0, e0), fmaf(d1, d1, e1)));
+        acc = fadd2(acc, fsub2(kpp, fadd2(k1, k2)));
     }
-    return acc;
+    return acc.x + acc.y;
 }
 template <int POL>
 __device__ __forceinline__ float duo_eval(float xi, float yhi, const float4* __restrict__ tile) {
@@ -158,9 +163,10 @@ __device__ __forceinline__ float duo_eval(float xi, float yhi, const float4* __r
     for (int s = 0; s < 32; ++s) {
         const float4 c = tile[s];
         const float dx = xi - c.x;
-        const float dx2 = dx * dx;
+        const float e = dx * dx;
         const float a = yhi - c.z, b = yhi - c.y;
-        acc += fmaf(-2.f, ksum_p<POL>(fmaf(b, b, dx2)), ksum_p<POL>(fmaf(a, a, dx2)));
+        const float2 k = ksum_p2<POL>(make_float2(fmaf(a, a, e), fmaf(b, b, e)));
+        acc += fmaf(-2.f, k.y, k.x);
     }
     return acc;
 }
