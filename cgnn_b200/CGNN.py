@@ -137,6 +137,26 @@ class CGNN(GraphModel):
         algorithms = {"HC": hill_climbing, "tabu": tabu_search, "EHC": exploratory_hill_climbing}
         return algorithms[alg](dag, data, self.infer_graph, **kwargs)
 
+    def generate(self, data, dag, n_samples=None, run=0, **kwargs):
+        """Fit the generative model of `dag` to `data` (one run) and draw a sample from it: the
+        `CGNN_tf.generate` of the reference (CGNN.py:155-160), which its model class never exposed.
+        Returns a DataFrame [n_samples, n_var] in the (standardised) units of the data."""
+        from . import runtime
+        from .plan import build_plan, n_params
+        data = DataFrame(scale(data.values), columns=data.columns)
+        cols = [c for c in data.columns if c in set(dag.get_list_nodes())]
+        plan = build_plan(dag, columns=cols)
+        X = np.ascontiguousarray(data[cols].values, np.float32)
+        eng = runtime.get_engines()[0]
+        uid = structure_uid(structure_key(dag)) + int(run)
+        kw = {k: v for k, v in kwargs.items() if k not in ("nb_runs", "nb_jobs")}
+        fit = eng.run_graph(X, [plan], n_runs=1, graph_uids=[uid], want_params=True, **kw)
+        h = int(kwargs.get("h_layer_dim", SETTINGS.h_layer_dim))
+        n = int(n_samples or X.shape[0])
+        noise = np.random.default_rng([int(SETTINGS.seed), uid >> 8, 0x6E]).standard_normal((plan["n_noise"], n))
+        sample = eng.graph_generate(plan, fit["params"][0, :n_params(plan, h)], noise, **kw)
+        return DataFrame(sample, columns=cols)
+
     def orient_undirected_graph(self, data, umg, **kwargs):
         """Orient a skeleton with the pairwise GNN, then improve it with CGNN (CGNN.py:369-381)."""
         warnings.warn("The pairwise GNN model is computed on each edge of the UMG "

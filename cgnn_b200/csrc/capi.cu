@@ -103,7 +103,7 @@ void cgnn_b200_destroy(cgnn_ctx* ctx) {
     cudaSetDevice(ctx->device);
     DevBuf* bufs[] = {&ctx->xy, &ctx->nrows, &ctx->inst, &ctx->scores, &ctx->noise, &ctx->init, &ctx->trace,
                       &ctx->pout, &ctx->counter, &ctx->dbg[0], &ctx->dbg[1], &ctx->dbg[2], &ctx->dbg[3], &ctx->dbg[4],
-                      &ctx->gT, &ctx->gdesc, &ctx->gtidx, &ctx->gsub, &ctx->gdata, &ctx->guid};
+                      &ctx->gT, &ctx->gdesc, &ctx->gtidx, &ctx->gsub, &ctx->gdata, &ctx->guid, &ctx->wz};
     for (DevBuf* b : bufs)
         if (b->p) cudaFree(b->p);
     if (ctx->ev0) cudaEventDestroy(ctx->ev0);
@@ -136,7 +136,7 @@ int cgnn_b200_device_info(const cgnn_ctx* ctx, int* n_sm, int* ctas_per_sm_pairw
 static int run_pairwise_impl(cgnn_ctx* ctx, const cgnn_hparams* hp, const float* xy, const int* n_rows, int n_pairs,
                              int ld_rows, int n_runs, unsigned long long uid_base, const float* noise,
                              const float* init_params, float* scores, float* loss_trace, float* params_out,
-                             float* const dbg_host[5], int dbg_steps) {
+                             float* const dbg_host[5], int dbg_steps, const float* fourier_wz = nullptr) {
     if (!ctx) return CGNN_ERR_ARG;
     ctx->err.clear();
     int rc = check_hp(ctx, hp);
@@ -215,6 +215,12 @@ static int run_pairwise_impl(cgnn_ctx* ctx, const cgnn_hparams* hp, const float*
         a.dbg_grad = dbg_dev[3]; a.dbg_params = dbg_dev[4];
     }
 
+    a.fast_k = hp->fast_mmd_vectors;
+    if (fourier_wz) {
+        if (a.fast_k < 1) return fail(ctx, CGNN_ERR_ARG, "fourier_wz given but hparams.fast_mmd_vectors is 0");
+        if ((rc = stage_in(ctx, ctx->wz, fourier_wz, sizeof(float) * size_t(n_inst) * epochs * 3 * 7 * a.fast_k, &dp))) return rc;
+        a.wz_ext = static_cast<const float*>(dp);
+    }
     a.n_inst = n_inst; a.ld_rows = ld_rows; a.np_max = 32 * ((max_n + 31) / 32);
     a.h = h; a.train_epochs = hp->train_epochs; a.test_epochs = hp->test_epochs; a.trace_every = hp->trace_every;
     a.lr = hp->learning_rate; a.init_std = hp->init_std;
@@ -222,7 +228,7 @@ static int run_pairwise_impl(cgnn_ctx* ctx, const cgnn_hparams* hp, const float*
                        (unsigned int)(hp->seed >> 32) ^ (unsigned int)(uid_base >> 32));
     a.uid_base = (unsigned int)(uid_base & 0xffffffffu);
 
-    const size_t smem = pw_smem_bytes(a.np_max, h);
+    const size_t smem = pw_smem_bytes(a.np_max, h, a.fast_k);
     if (smem > size_t(ctx->prop.sharedMemPerBlockOptin))
         return fail(ctx, CGNN_ERR_LIMIT, "instance needs %zu B of shared memory, device allows %zu", smem,
                     size_t(ctx->prop.sharedMemPerBlockOptin));
@@ -262,8 +268,8 @@ int cgnn_b200_run_pairwise(cgnn_ctx* ctx, const cgnn_hparams* hp, const float* x
 }
 
 int cgnn_b200_pairwise_step_debug(cgnn_ctx* ctx, const cgnn_hparams* hp, const float* xy, int n_rows, int n_steps,
-                                  const float* noise, const float* init_params, float* out_loss, float* out_yhat,
-                                  float* out_dldy, float* out_grad, float* out_params) {
+                                  const float* noise, const float* init_params, const float* fourier_wz, float* out_loss,
+                                  float* out_yhat, float* out_dldy, float* out_grad, float* out_params) {
     if (!ctx) return CGNN_ERR_ARG;
     if (!hp) return fail(ctx, CGNN_ERR_ARG, "hparams is NULL");
     if (!noise || !init_params) return fail(ctx, CGNN_ERR_ARG, "step_debug needs caller-supplied noise and parameters");
@@ -274,7 +280,7 @@ int cgnn_b200_pairwise_step_debug(cgnn_ctx* ctx, const cgnn_hparams* hp, const f
     h2.trace_every = 0;
     float* dbg[5] = {out_loss, out_yhat, out_dldy, out_grad, out_params};
     return run_pairwise_impl(ctx, &h2, xy, &n_rows, 1, n_rows, 1, 0ULL, noise, init_params, nullptr, nullptr, nullptr, dbg,
-                             n_steps);
+                             n_steps, fourier_wz);
 }
 
 
@@ -366,6 +372,8 @@ extern "C" int cgnn_b200_run_pairwise_noalloc(int device, void* stream, const cg
         return na_fail(errbuf, errbuf_len, CGNN_ERR_LIMIT, "h_layer_dim=%d outside [1,%d]", hp->h_layer_dim, CGNN_MAX_H);
     if (hp->train_epochs < 0 || hp->test_epochs < 0 || hp->exp_policy < 0 || hp->exp_policy > 3)
         return na_fail(errbuf, errbuf_len, CGNN_ERR_ARG, "bad epoch count or exp_policy");
+    if (hp->fast_mmd_vectors < 0 || hp->fast_mmd_vectors > CGNN_MAX_FAST_VECTORS)
+        return na_fail(errbuf, errbuf_len, CGNN_ERR_LIMIT, "fast_mmd_vectors=%d outside [0,%d]", hp->fast_mmd_vectors, CGNN_MAX_FAST_VECTORS);
     if (n_pairs < 1 || n_runs < 1 || n_rows < 1) return na_fail(errbuf, errbuf_len, CGNN_ERR_ARG, "n_pairs, n_runs, n_rows must be >= 1");
     if (n_rows > CGNN_MAX_ROWS_PAIRWISE)
         return na_fail(errbuf, errbuf_len, CGNN_ERR_LIMIT, "n_rows=%d exceeds CGNN_MAX_ROWS_PAIRWISE=%d", n_rows, CGNN_MAX_ROWS_PAIRWISE);
@@ -405,8 +413,9 @@ extern "C" int cgnn_b200_run_pairwise_noalloc(int device, void* stream, const cg
     a.key = make_uint2((unsigned int)(hp->seed & 0xffffffffu), (unsigned int)(hp->seed >> 32) ^ (unsigned int)(uid_base >> 32));
     a.uid_base = (unsigned int)(uid_base & 0xffffffffu);
     a.scores = d_scores;
+    a.fast_k = hp->fast_mmd_vectors;
 
-    const size_t smem = pw_smem_bytes(a.np_max, a.h);
+    const size_t smem = pw_smem_bytes(a.np_max, a.h, a.fast_k);
     if (smem > size_t(smem_optin)) return na_fail(errbuf, errbuf_len, CGNN_ERR_LIMIT, "instance needs %zu B of shared memory", smem);
     const int per_sm = pairwise_occupancy(hp->exp_policy, smem);
     if (per_sm < 1) return na_fail(errbuf, errbuf_len, CGNN_ERR_CUDA, "pairwise kernel cannot be resident");

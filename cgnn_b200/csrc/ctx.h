@@ -28,6 +28,7 @@ struct cgnn_ctx {
     // staging buffers (grow-only)
     DevBuf xy, nrows, inst, scores, noise, init, trace, pout, counter, dbg[5];
     DevBuf gT, gdesc, gtidx, gsub, gdata, guid;      // graph path
+    DevBuf wz;                                       // Fourier parity mode
 };
 
 static inline int fail(cgnn_ctx* c, int code, const char* fmt, ...) {
@@ -98,5 +99,7 @@ static inline int check_hp(cgnn_ctx* ctx, const cgnn_hparams* hp) {
         return fail(ctx, CGNN_ERR_LIMIT, "h_layer_dim=%d outside [1,%d]", hp->h_layer_dim, CGNN_MAX_H);
     if (hp->train_epochs < 0 || hp->test_epochs < 0) return fail(ctx, CGNN_ERR_ARG, "negative epoch count");
     if (hp->exp_policy < 0 || hp->exp_policy > 3) return fail(ctx, CGNN_ERR_ARG, "exp_policy=%d unknown", hp->exp_policy);
+    if (hp->fast_mmd_vectors < 0 || hp->fast_mmd_vectors > CGNN_MAX_FAST_VECTORS)
+        return fail(ctx, CGNN_ERR_LIMIT, "fast_mmd_vectors=%d outside [0,%d]", hp->fast_mmd_vectors, CGNN_MAX_FAST_VECTORS);
     return 0;
 }

@@ -474,11 +474,11 @@ __global__ void __launch_bounds__(GR_NT, 1) graph_kernel(const GraphArgs a) {
                     for (int q = tid; q < P; q += GR_NT) a.dbg_params[size_t(it) * P + q] = s.theta[gr_pad_index(*s.desc, q, h, HP)];
                 }
             }
-            if (it == a.train_epochs - 1 && a.params_out) {
-                __syncthreads();
-                for (int q = tid; q < P; q += GR_NT)
-                    a.params_out[size_t(out) * a.ld_params + q] = s.theta[gr_pad_index(*s.desc, q, h, HP)];
-            }
+        }
+        if (a.params_out) {            // evaluation does not touch the parameters: these are the trained ones
+            __syncthreads();
+            for (int q = tid; q < P; q += GR_NT)
+                a.params_out[size_t(out) * a.ld_params + q] = s.theta[gr_pad_index(*s.desc, q, h, HP)];
         }
         if (tid == 0 && a.scores) a.scores[out] = a.test_epochs > 0 ? float(score_sum / double(a.test_epochs)) : 0.f;
     }

@@ -52,6 +52,8 @@ static int run_graph_impl(cgnn_ctx* ctx, const cgnn_hparams* hp, const float* da
     if (rc) return rc;
     if (hp->h_layer_dim > CGNN_MAX_H_GRAPH)
         return fail(ctx, CGNN_ERR_LIMIT, "graph path: h_layer_dim=%d exceeds CGNN_MAX_H_GRAPH=%d", hp->h_layer_dim, CGNN_MAX_H_GRAPH);
+    if (hp->fast_mmd_vectors != 0)
+        return fail(ctx, CGNN_ERR_LIMIT, "the random-feature loss (use_Fast_MMD) is implemented for the pairwise path only");
     if (!data || !gb) return fail(ctx, CGNN_ERR_ARG, "data / graph batch is NULL");
     if (!gb->node_col || !gb->n_parents || !gb->n_inputs || !gb->in_ptr || !gb->in_idx)
         return fail(ctx, CGNN_ERR_ARG, "graph batch has a NULL array");

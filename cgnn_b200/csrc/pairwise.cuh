@@ -60,15 +60,19 @@ struct PairwiseArgs {
     int*   counter;           // work queue head (scratch)
     // parity probe (single instance): any may be NULL
     float *dbg_loss, *dbg_yhat, *dbg_dldy, *dbg_grad, *dbg_params;
+    // random-feature ("Fourier") MMD, Loss.py:35-56 (SETTINGS.use_Fast_MMD): fast_k = nb_vectors_approx_MMD, 0 = off
+    int fast_k;
+    const float* wz_ext;      // NULL (in-kernel Philox) or [n_inst][epochs][3][7*fast_k]: the matrix of Loss.py:35-37
 };
 
 struct PwSmem {
     float4* Qd; float* xs; float* es; float* yh; long long* g64;
     float* theta; float* am; float* av; float* part; double* red;
     int part_stride;
+    float4* feat; long long* et; long long* ep;      // Fourier mode only: features (wx/S, wy/S, phase, coef), column sums
 };
 
-__host__ __device__ inline size_t pw_smem_bytes(int np_max, int h) {
+__host__ __device__ inline size_t pw_smem_bytes(int np_max, int h, int fast_k = 0) {
     int nchunk = (h + 7) / 8;
     int P = 4 * h + 1;
     int Pp = (P + 3) & ~3;
@@ -79,6 +83,8 @@ __host__ __device__ inline size_t pw_smem_bytes(int np_max, int h) {
     b += size_t(np_max) * 4 * 3;                 // xs, es, yh
     b += size_t(Pp) * 4 * 3;                     // theta, m, v
     b += size_t(PW_NW) * (nchunk * 32 + 4) * 4;  // per-warp partial gradient sums
+    b = (b + 15) & ~size_t(15);
+    b += size_t(7 * fast_k) * (16 + 8 + 8);      // Fourier mode: feat, et, ep
     return (b + 15) & ~size_t(15);
 }
 
@@ -240,6 +246,86 @@ __device__ double tt_pass(const float4* __restrict__ Qd, int N, int NB, int warp
     return lsum;
 }
 
+// ---- random-feature ("Fourier") MMD: Loss.py:35-56 ---------------------------------------------
+// F = 7k features f with frequency w_f = 2 gamma_g N(0,1)^2 (g = f / k) and phase b_f = U(0, 2 pi), redrawn
+// at every step (they are graph ops in the reference).  loss = sum_f (e1_f - e2_f)^2 with
+// e_f = sqrt(2/k) mean_i cos(w_f . row_i + b_f) over the observed (e1) and the generated (e2) rows.
+constexpr uint32_t STREAM_FEAT = 7u;
+constexpr int PW_FCHUNKS = 8;            // row chunks per feature in the column-sum pass
+
+__device__ __forceinline__ float pw_turn_reduce(float z) {       // z radians -> equivalent angle in [-pi, pi]
+    const float t = z * 0.15915494309189535f;
+    return (t - rintf(t)) * 6.283185307179586f;
+}
+
+// draw (or fetch) the features of this step and clear the column sums
+__device__ __forceinline__ void pw_fourier_features(const PwSmem& s, const PairwiseArgs& a, int F, int step,
+                                                    unsigned int uid, const float* wz_step, int tid) {
+    const float gam[7] = {G0, G1, G2, G3, G4, G5, G6};
+    for (int f = tid; f < F; f += PW_NT) {
+        float wx, wy, b;
+        if (wz_step) { wx = wz_step[f]; wy = wz_step[F + f]; b = wz_step[2 * F + f]; }
+        else {
+            const uint4 r = philox4x32_10(make_uint4(f, step, STREAM_FEAT, uid), a.key);
+            const float4 n = normal4(r);
+            const float g2 = 2.0f * gam[f / a.fast_k];
+            wx = g2 * n.x; wy = g2 * n.y;
+            b = 6.283185307179586f * u01(r.z ^ 0x9E3779B9u);
+        }
+        s.feat[f] = make_float4(wx * (1.0f / CGNN_PRESCALE), wy * (1.0f / CGNN_PRESCALE), b, wy);
+        s.et[f] = 0; s.ep[f] = 0;
+    }
+}
+
+// column sums of cos over the rows: work item = (feature, row chunk); fixed-point accumulation
+__device__ __forceinline__ void pw_fourier_colsums(const PwSmem& s, int N, int NB, int F, int tid) {
+    const int tiles_per_chunk = (NB + PW_FCHUNKS - 1) / PW_FCHUNKS;
+    for (int w = tid; w < F * PW_FCHUNKS; w += PW_NT) {
+        const int chunk = w / F, f = w - chunk * F;
+        const float4 ft = s.feat[f];
+        float st = 0.f, sp = 0.f;
+        const int J0 = chunk * tiles_per_chunk, J1 = min(J0 + tiles_per_chunk, NB);
+        for (int J = J0; J < J1; ++J) {
+            const int nt = min(32, N - 32 * J);
+#pragma unroll 4
+            for (int t = 0; t < nt; ++t) {
+                const float4 c = s.Qd[64 * J + t];
+                const float zx = fmaf(ft.x, c.x, ft.z);
+                st += __cosf(pw_turn_reduce(fmaf(ft.y, c.y, zx)));
+                sp += __cosf(pw_turn_reduce(fmaf(ft.y, c.z, zx)));
+            }
+        }
+        if (J1 > J0) { fx_add(&s.et[f], double(st)); fx_add(&s.ep[f], double(sp)); }
+    }
+}
+
+// e1, e2 -> loss share of this thread; the gradient coefficient replaces feat.w
+__device__ __forceinline__ double pw_fourier_coefs(const PwSmem& s, int N, int F, int k, int tid) {
+    const double norm = sqrt(2.0 / double(k)) / double(N);
+    double part = 0.0;
+    for (int f = tid; f < F; f += PW_NT) {
+        const double diff = norm * (fx_get(&s.et[f]) - fx_get(&s.ep[f]));       // e1_f - e2_f
+        part += diff * diff;
+        s.feat[f].w = float(2.0 * diff * norm) * s.feat[f].w;   // dLoss/d yhat_i = sum_f coef_f sin(z_if)
+    }
+    return part;
+}
+
+// dLoss/d yhat_i for every row: thread = row, all features broadcast from shared memory
+__device__ __forceinline__ void pw_fourier_rowgrad(const PwSmem& s, int N, int F, int tid) {
+    for (int i = tid; i < N; i += PW_NT) {
+        const float4 c = s.Qd[pw_slot_of_row(i)];
+        float g = 0.f;
+#pragma unroll 4
+        for (int f = 0; f < F; ++f) {
+            const float4 ft = s.feat[f];
+            const float z = fmaf(ft.y, c.z, fmaf(ft.x, c.x, ft.z));
+            g = fmaf(ft.w, __sinf(pw_turn_reduce(z)), g);
+        }
+        fx_add(&s.g64[i], double(g));
+    }
+}
+
 // Block-wide sum of per-lane doubles in a fixed order (deterministic). Result valid in thread 0.
 __device__ __forceinline__ double block_sum(double v, double* red, int warp, int lane) {
     v = warp_sum(v);
@@ -292,8 +378,8 @@ __device__ __forceinline__ void pw_forward(const PwSmem& s, const PairwiseArgs& 
 }
 
 // Generator backward: per-warp partial parameter gradients into s.part (deterministic tree).
-__device__ __forceinline__ void pw_backward_partials(const PwSmem& s, int N, int NP, int h, int tid, int warp, int lane) {
-    const float scale = 4.0f / (float(N) * float(N) * CGNN_PRESCALE);
+__device__ __forceinline__ void pw_backward_partials(const PwSmem& s, int N, int NP, int h, int tid, int warp, int lane,
+                                                     float scale) {
     const int nchunk = (h + 7) >> 3;
     float* mine = s.part + warp * s.part_stride;
     for (int c = 0; c < nchunk; ++c) mine[32 * c + lane] = 0.f;
@@ -366,7 +452,14 @@ __global__ void __launch_bounds__(PW_NT, PW_MIN_CTAS) pairwise_kernel(const Pair
         s.av = reinterpret_cast<float*>(p);       p += size_t(Pp) * 4;
         s.part = reinterpret_cast<float*>(p);
         s.part_stride = nchunk * 32 + 4;
+        size_t used = size_t(p - smem_raw) + size_t(PW_NW) * s.part_stride * 4;
+        used = (used + 15) & ~size_t(15);
+        s.feat = reinterpret_cast<float4*>(smem_raw + used);
+        s.et = reinterpret_cast<long long*>(smem_raw + used + size_t(7 * a.fast_k) * 16);
+        s.ep = s.et + 7 * a.fast_k;
     }
+    const int F = 7 * a.fast_k;
+    const bool fast = a.fast_k > 0;
     double& s_TT = s.red[PW_NW];
 
     for (;;) {
@@ -413,11 +506,13 @@ __global__ void __launch_bounds__(PW_NT, PW_MIN_CTAS) pairwise_kernel(const Pair
         }
         __syncthreads();
         // ---- TT: constant per instance, fp64 accumulation ----------------------------------
-        {
+        if (!fast) {
             const double part = tt_pass<POL>(s.Qd, N, NB, warp, lane);
             const double tt = block_sum(part, s.red, warp, lane);
             if (tid == 0) s_TT = tt;
         }
+        const float* wz = (fast && a.wz_ext) ? a.wz_ext + size_t(out) * epochs * 3 * F : nullptr;
+        const float gscale = fast ? 1.0f : 4.0f / (float(N) * float(N) * CGNN_PRESCALE);
         // beta^t accumulators.  TF keeps them in fp32, which puts a 6e-6 relative error on every step size
         // ((1 - 0.999f^t) inherits fp32(0.999)'s rounding); thread 0 keeps them in fp64 in shared memory.
         if (tid == 0) { s.red[PW_NW + 1] = 1.0; s.red[PW_NW + 2] = 1.0; }
@@ -434,25 +529,38 @@ __global__ void __launch_bounds__(PW_NT, PW_MIN_CTAS) pairwise_kernel(const Pair
             pw_forward(s, a, N, NP, h, it, uid, noise ? noise + size_t(it) * a.ld_rows : nullptr, tid);
             __syncthreads();
             const bool traced = a.dbg_loss || (a.trace && a.trace_every > 0 && it % a.trace_every == 0);
-            if (traced) {   // loss fetched with the train op is the pre-update loss (GNN.py:93-94)
-                const double part = mmd_pass<POL, false>(s.Qd, nullptr, N, NB, warp, lane);
-                const double sum = block_sum(part, s.red, warp, lane);
+            if (a.dbg_yhat) for (int i = tid; i < N; i += PW_NT) a.dbg_yhat[size_t(it) * N + i] = s.yh[i];
+            if (fast) {   // random-feature loss: the loss value is a by-product of the gradient
+                pw_fourier_features(s, a, F, it, uid, wz ? wz + size_t(it) * 3 * F : nullptr, tid);
+                __syncthreads();
+                pw_fourier_colsums(s, N, NB, F, tid);
+                __syncthreads();
+                const double sum = block_sum(pw_fourier_coefs(s, N, F, a.fast_k, tid), s.red, warp, lane);
                 if (tid == 0) {
-                    const float loss = float((sum + s_TT) * invN2);
+                    const float loss = float(sum);
                     if (a.trace) a.trace[size_t(out) * epochs + it] = loss;
                     if (a.dbg_loss) a.dbg_loss[it] = loss;
                 }
-            } else if (a.trace && tid == 0) {
-                a.trace[size_t(out) * epochs + it] = __int_as_float(0x7fc00000);
+                __syncthreads();
+                pw_fourier_rowgrad(s, N, F, tid);
+            } else {
+                if (traced) {   // loss fetched with the train op is the pre-update loss (GNN.py:93-94)
+                    const double part = mmd_pass<POL, false>(s.Qd, nullptr, N, NB, warp, lane);
+                    const double sum = block_sum(part, s.red, warp, lane);
+                    if (tid == 0) {
+                        const float loss = float((sum + s_TT) * invN2);
+                        if (a.trace) a.trace[size_t(out) * epochs + it] = loss;
+                        if (a.dbg_loss) a.dbg_loss[it] = loss;
+                    }
+                } else if (a.trace && tid == 0) {
+                    a.trace[size_t(out) * epochs + it] = __int_as_float(0x7fc00000);
+                }
+                mmd_pass<POL, true>(s.Qd, s.g64, N, NB, warp, lane);
             }
-            if (a.dbg_yhat) for (int i = tid; i < N; i += PW_NT) a.dbg_yhat[size_t(it) * N + i] = s.yh[i];
-            mmd_pass<POL, true>(s.Qd, s.g64, N, NB, warp, lane);
             __syncthreads();
-            if (a.dbg_dldy) {
-                const float scale = 4.0f / (float(N) * float(N) * CGNN_PRESCALE);
-                for (int i = tid; i < N; i += PW_NT) a.dbg_dldy[size_t(it) * N + i] = float(fx_get(&s.g64[i])) * scale;
-            }
-            pw_backward_partials(s, N, NP, h, tid, warp, lane);
+            if (a.dbg_dldy)
+                for (int i = tid; i < N; i += PW_NT) a.dbg_dldy[size_t(it) * N + i] = float(fx_get(&s.g64[i])) * gscale;
+            pw_backward_partials(s, N, NP, h, tid, warp, lane, gscale);
             __syncthreads();
             for (int p = tid; p < P; p += PW_NT) {
                 const int slot = pw_slot(p, h);
@@ -478,10 +586,18 @@ __global__ void __launch_bounds__(PW_NT, PW_MIN_CTAS) pairwise_kernel(const Pair
             pw_forward(s, a, N, NP, h, a.train_epochs + it, uid,
                        noise ? noise + size_t(a.train_epochs + it) * a.ld_rows : nullptr, tid);
             __syncthreads();
-            const double part = mmd_pass<POL, false>(s.Qd, nullptr, N, NB, warp, lane);
-            const double sum = block_sum(part, s.red, warp, lane);
+            double sum;
+            if (fast) {
+                pw_fourier_features(s, a, F, a.train_epochs + it, uid, wz ? wz + size_t(a.train_epochs + it) * 3 * F : nullptr, tid);
+                __syncthreads();
+                pw_fourier_colsums(s, N, NB, F, tid);
+                __syncthreads();
+                sum = block_sum(pw_fourier_coefs(s, N, F, a.fast_k, tid), s.red, warp, lane);
+            } else {
+                sum = block_sum(mmd_pass<POL, false>(s.Qd, nullptr, N, NB, warp, lane), s.red, warp, lane);
+            }
             if (tid == 0) {
-                const float loss = float((sum + s_TT) * invN2);    // the reference fetches an fp32 loss ...
+                const float loss = fast ? float(sum) : float((sum + s_TT) * invN2);    // the reference fetches an fp32 loss ...
                 score_sum += double(loss);                         // ... and sums it in a Python float
                 if (a.trace) a.trace[size_t(out) * epochs + a.train_epochs + it] = loss;
             }

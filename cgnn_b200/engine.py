@@ -43,6 +43,8 @@ def make_hparams(**kw):
     hp.init_std = float(kw.get("init_std", SETTINGS.init_weights))
     hp.exp_policy = int(kw.get("exp_policy", SETTINGS.exp_policy))
     hp.trace_every = int(kw.get("trace_every", 0))
+    fast = kw.get("use_Fast_MMD", SETTINGS.use_Fast_MMD)            # GNN.py:47-48, CGNN.py:50-51
+    hp.fast_mmd_vectors = int(kw.get("nb_vectors_approx_MMD", SETTINGS.nb_vectors_approx_MMD)) if fast else 0
     hp.seed = int(kw.get("seed", SETTINGS.seed)) & 0xFFFFFFFFFFFFFFFF
     return hp
 
@@ -133,9 +135,13 @@ class Engine:
         self._check(rc, "cgnn_b200_run_pairwise")
         return dict(scores=scores, trace=trace, params=pout)
 
-    def pairwise_step_debug(self, xy, noise, init_params, **kw):
-        """Parity probe: consecutive train steps of ONE instance (column 0 = cause)."""
+    def pairwise_step_debug(self, xy, noise, init_params, fourier_wz=None, **kw):
+        """Parity probe: consecutive train steps of ONE instance (column 0 = cause).
+        fourier_wz [n_steps, 3, 7k]: with use_Fast_MMD=True, the random matrix of Loss.py:35-37 per step."""
         hp = make_hparams(**kw)
+        if fourier_wz is not None:
+            fourier_wz = np.ascontiguousarray(fourier_wz, np.float32)
+            assert fourier_wz.shape == (noise.shape[0], 3, 7 * hp.fast_mmd_vectors)
         xy = np.ascontiguousarray(xy, np.float32)
         noise = np.ascontiguousarray(noise, np.float32)
         init_params = np.ascontiguousarray(init_params, np.float32)
@@ -146,7 +152,7 @@ class Engine:
                    dldy=np.empty((n_steps, n_rows), np.float32), grad=np.empty((n_steps, P), np.float32),
                    params=np.empty((n_steps, P), np.float32))
         rc = self._lib.cgnn_b200_pairwise_step_debug(self._h, C.byref(hp), _ptr(xy), n_rows, n_steps, _ptr(noise),
-                                                     _ptr(init_params), _ptr(out["loss"]), _ptr(out["yhat"]),
+                                                     _ptr(init_params), _ptr(fourier_wz), _ptr(out["loss"]), _ptr(out["yhat"]),
                                                      _ptr(out["dldy"]), _ptr(out["grad"]), _ptr(out["params"]))
         self._check(rc, "cgnn_b200_pairwise_step_debug")
         return out
@@ -217,3 +223,12 @@ class Engine:
                                                   _ptr(out["dldp"]), _ptr(out["grad"]), _ptr(out["params"]))
         self._check(rc, "cgnn_b200_graph_step_debug")
         return out
+
+    def graph_generate(self, plan, params, noise, **kw):
+        """One sample of the generative model (CGNN_tf.generate, CGNN.py:155-160): the generated matrix
+        [N, n_var] for given parameters (flat, caller-visible layout) and noise [n_noise, N]."""
+        noise = np.ascontiguousarray(noise, np.float32)
+        n_rows = noise.shape[1]
+        dummy = np.zeros((n_rows, plan["n_var"]), np.float32)
+        out = self.graph_step_debug(dummy, plan, noise[None], np.asarray(params, np.float32), **kw)
+        return out["pred"][0]

@@ -32,6 +32,7 @@ extern "C" {
 #define CGNN_MAX_H             64       /* hidden width limit (reference default 20, scripts use 30) */
 #define CGNN_MAX_H_GRAPH       32       /* hidden width limit of the graph path (reference default 20) */
 #define CGNN_MAX_VARS          32       /* variables (columns) per graph */
+#define CGNN_MAX_FAST_VECTORS  256      /* nb_vectors_approx_MMD limit of the random-feature loss (reference default 100) */
 #define CGNN_MAX_ROWS_GRAPH    1536     /* rows per graph instance after subsampling (SETTINGS.max_nb_points = 1500) */
 
 typedef enum cgnn_status {
@@ -59,7 +60,9 @@ typedef struct cgnn_hparams {
                                  3 = three (+ gamma 5 = 5th power of gamma 1) */
     int   trace_every;        /* >0: also compute the (pre-update) training loss on every trace_every-th
                                  train step into loss_trace (GNN.py:98-102 prints every 100th); 0 = never */
-    int   reserved0;
+    int   fast_mmd_vectors;   /* 0: Gaussian-kernel MMD (SETTINGS.use_Fast_MMD = False).  k > 0: the random-feature loss
+                                 of Loss.py:35-56 with k = SETTINGS.nb_vectors_approx_MMD vectors per bandwidth
+                                 (pairwise path; k <= CGNN_MAX_FAST_VECTORS) */
     unsigned long long seed;  /* engine Philox seed.  The reference is unseeded (no hit for "seed" in its tree). */
 } cgnn_hparams;
 
@@ -117,11 +120,13 @@ int  cgnn_b200_run_pairwise(cgnn_ctx* ctx, const cgnn_hparams* hp,
  * each sess.run (GNN.py:93-96): the loss before the update, the generated column, dLoss/d out_y,
  * the parameter gradient and the parameters after the Adam update.  Runs the production kernel.
  *   xy [n_rows][2], noise [n_steps][n_rows], init_params [4h+1]
+ *   fourier_wz  NULL, or - with hp->fast_mmd_vectors = k - the random matrix of Loss.py:35-37 for every step,
+ *               [n_steps][3][7k] (rows: frequency on the cause, frequency on the effect, phase)
  *   out_loss [n_steps], out_yhat [n_steps][n_rows], out_dldy [n_steps][n_rows],
  *   out_grad [n_steps][4h+1], out_params [n_steps][4h+1]    (any of them may be NULL) */
 int  cgnn_b200_pairwise_step_debug(cgnn_ctx* ctx, const cgnn_hparams* hp,
                                    const float* xy, int n_rows, int n_steps,
-                                   const float* noise, const float* init_params,
+                                   const float* noise, const float* init_params, const float* fourier_wz,
                                    float* out_loss, float* out_yhat, float* out_dldy,
                                    float* out_grad, float* out_params);
 

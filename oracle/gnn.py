@@ -48,33 +48,42 @@ def loss_torch(theta, data, e, h):
     return mmd_loss_literal(torch.cat([x, y], 1), torch.cat([x, out_y], 1)), out_y
 
 
-def step_debug(theta0, data, e, h, dtype=torch.float64):
-    """One training evaluation: returns dict(loss, out_y, dloss_dout, grad) (no update)."""
+def step_debug(theta0, data, e, h, dtype=torch.float64, wz=None, k=None):
+    """One training evaluation: returns dict(loss, out_y, dloss_dout, grad) (no update).
+    wz [3, 7k]: use the random-feature loss of GNN.py:69-70 (use_Fast_MMD) with that matrix."""
     th = torch.as_tensor(np.asarray(theta0), dtype=dtype).clone().requires_grad_(True)
     d = torch.as_tensor(np.asarray(data), dtype=dtype)
     ee = torch.as_tensor(np.asarray(e), dtype=dtype).reshape(-1, 1)
-    loss, out_y = loss_torch(th, d, ee, h)
+    if wz is None:
+        loss, out_y = loss_torch(th, d, ee, h)
+    else:
+        from .mmd import fourier_mmd_literal
+        x, y = d[:, :1], d[:, 1:2]
+        out_y = forward_torch(th, x, ee, h)
+        loss = fourier_mmd_literal(torch.cat([x, y], 1), torch.cat([x, out_y], 1),
+                                   torch.as_tensor(np.asarray(wz), dtype=dtype), k)
     out_y.retain_grad()
     loss.backward()
     return dict(loss=float(loss.detach()), out_y=out_y.detach().numpy()[:, 0].copy(),
                 dloss_dout=out_y.grad.numpy()[:, 0].copy(), grad=th.grad.numpy().copy())
 
 
-def train(theta0, data, noise, h, lr=0.01, dtype=torch.float64):
-    """GNN.py:92-96.  noise: [train_epochs, N].  Returns (theta, losses[train_epochs], thetas per step)."""
+def train(theta0, data, noise, h, lr=0.01, dtype=torch.float64, wz=None, k=None):
+    """GNN.py:92-96.  noise: [train_epochs, N]; wz: None or [train_epochs, 3, 7k] (use_Fast_MMD).
+    Returns (theta, losses[train_epochs], thetas per step)."""
     npdt = np.float64 if dtype == torch.float64 else np.float32
     theta = np.asarray(theta0, npdt).copy()
     opt = TFAdam(theta.size, lr, npdt)
     losses, trail = [], []
     for it in range(noise.shape[0]):
-        r = step_debug(theta, data, noise[it], h, dtype)
+        r = step_debug(theta, data, noise[it], h, dtype, None if wz is None else wz[it], k)
         losses.append(r["loss"])
         theta = opt.step(theta, r["grad"].astype(npdt)).astype(npdt)
         trail.append(theta.copy())
     return theta, np.array(losses), trail
 
 
-def evaluate(theta, data, noise, h, dtype=torch.float64):
+def evaluate(theta, data, noise, h, dtype=torch.float64, wz=None, k=None):
     """GNN.py:115-126.  noise: [test_epochs, N].  Returns (mean, per-epoch losses)."""
     th = torch.as_tensor(np.asarray(theta), dtype=dtype)
     d = torch.as_tensor(np.asarray(data), dtype=dtype)
@@ -82,7 +91,13 @@ def evaluate(theta, data, noise, h, dtype=torch.float64):
     with torch.no_grad():
         for it in range(noise.shape[0]):
             ee = torch.as_tensor(np.asarray(noise[it]), dtype=dtype).reshape(-1, 1)
-            out.append(float(loss_torch(th, d, ee, h)[0]))
+            if wz is None:
+                out.append(float(loss_torch(th, d, ee, h)[0]))
+            else:
+                from .mmd import fourier_mmd_literal
+                x, y = d[:, :1], d[:, 1:2]
+                out.append(float(fourier_mmd_literal(torch.cat([x, y], 1), torch.cat([x, forward_torch(th, x, ee, h)], 1),
+                                                     torch.as_tensor(np.asarray(wz[it]), dtype=dtype), k)))
     avg = 0.0
     for s in out:                       # GNN.py:113,120: running sum then / test_epochs
         avg += s

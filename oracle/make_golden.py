@@ -36,6 +36,7 @@ def _split_draws(tf, n_init_tensors):
 
 
 def golden_mmd(tf, ref):
+    from oracle import GAMMAS
     rng = np.random.default_rng(11)
     out = {}
     for k, (n, d) in enumerate(((50, 2), (37, 5), (64, 22))):
@@ -49,6 +50,20 @@ def golden_mmd(tf, ref):
         ctx_loss = loss.value(tf._Ctx(None, "run"))
         (g,) = torch.autograd.grad(ctx_loss, [pv.tensor])
         out.update({"t%d" % k: t, "p%d" % k: p, "loss%d" % k: val, "grad%d" % k: g.numpy()})
+        tf.reset_default_graph()
+    # the random-feature loss (Loss.py:35-56): record the matrix the reference's rp() drew
+    for k, (n, d, nv) in enumerate(((40, 2, 6), (33, 5, 4))):
+        t = rng.normal(size=(n, d))
+        p = t[rng.permutation(n)] * 0.9 + 0.3 * rng.normal(size=(n, d))
+        tf.reset(seed=40 + k)
+        pv = tf.Variable(tf.constant(p))
+        loss = ref["Loss"].Fourier_MMD_Loss_tf(tf.constant(t), pv, nv)
+        sess = tf.Session()
+        sess.run(tf.global_variables_initializer())
+        val = sess.run(loss)
+        draws = [d_[2] for d_ in tf.DRAWS if d_[1] == "run"]
+        wz = np.concatenate([np.concatenate([2.0 * g * dr for g, dr in zip(GAMMAS, draws[:7])], 0), draws[7]], 1).T
+        out.update({"ft%d" % k: t, "fp%d" % k: p, "fwz%d" % k: wz, "fk%d" % k: nv, "floss%d" % k: val})
         tf.reset_default_graph()
     np.savez_compressed(os.path.join(OUT, "ref_shim_mmd.npz"), **out)
 
@@ -72,6 +87,24 @@ def golden_pairwise(tf, ref):
         assert noise.shape == (tr + te, n) and losses.shape == (tr + te,)
         out.update({tag + "_data": data, tag + "_h": h, tag + "_train": tr, tag + "_test": te, tag + "_theta0": theta0,
                     tag + "_noise": noise, tag + "_losses": losses, tag + "_score": score})
+    # the same generator trained against the random-feature loss (use_Fast_MMD=True, GNN.py:69-70)
+    from oracle import GAMMAS
+    n, h, tr, te, nv = 72, 6, 9, 4, 5
+    data = np.stack([df["A"][2][:n], df["B"][2][:n]], 1).astype("float32")
+    tf.reset(seed=12)
+    model = ref["GNN"].GNN_tf(n, h_layer_dim=h, learning_rate=0.01, init_std=0.05, use_Fast_MMD=True, nb_vectors_approx_MMD=nv)
+    _quiet(model.train, data, verbose=False, train_epochs=tr)
+    score = _quiet(model.evaluate, data, verbose=False, test_epochs=te)
+    init, runs = _split_draws(tf, 4)
+    W_in, b_in, W_out, b_out = init
+    ids = sorted(set(d[0] for d in runs))                 # creation order: e, then rp(): 7 normal blocks, the phases
+    per = {i: [d[2] for d in runs if d[0] == i] for i in ids}
+    noise = np.stack([a[:, 0] for a in per[ids[0]]])
+    wz = np.stack([np.concatenate([np.concatenate([2.0 * g * per[ids[1 + j]][s] for j, g in enumerate(GAMMAS)], 0),
+                                   per[ids[8]][s]], 1).T for s in range(tr + te)])
+    losses = np.array([r[0] for r in tf.RUN_LOG if len(r)], dtype=np.float64)
+    out.update(dict(f_data=data, f_h=h, f_train=tr, f_test=te, f_k=nv, f_noise=noise, f_wz=wz, f_losses=losses, f_score=score,
+                    f_theta0=np.concatenate([W_in[0], W_in[1], b_in, W_out[:, 0], b_out])))
     # both directions through tf_run_instance (column swap of GNN.py:162)
     n, h, tr, te = 64, 5, 6, 3
     data = np.stack([df["A"][1][:n], df["B"][1][:n]], 1).astype("float32")

@@ -79,3 +79,25 @@ def mmd_grad_analytic(xy_true: np.ndarray, xy_pred: np.ndarray) -> np.ndarray:
     Wpp = sum(g * np.exp(-g * Dpp) for g in GAMMAS)
     grad = (Wpt.sum(1)[:, None] * p - Wpt @ t) - (Wpp.sum(1)[:, None] * p - Wpp @ p)
     return 4.0 / (N * N) * grad
+
+
+# ---- random-feature ("Fourier") MMD: the use_Fast_MMD=True alternative (Loss.py:35-56) ---------------
+def rp_literal(k, d, rng):
+    """Loss.py:35-37: W = [2*gamma_i * N(0,1)[k,d] for the 7 gammas ; U(0, 2 pi)[7k,1]]^T -> [d+1, 7k].
+    rng: numpy RandomState-like with standard_normal / uniform (draw order as the TF graph creates the ops)."""
+    blocks = [2.0 * g * rng.standard_normal((k, d)) for g in GAMMAS]
+    phase = rng.uniform(0.0, 2.0 * np.pi, (k * len(GAMMAS), 1))
+    return np.concatenate([np.concatenate(blocks, 0), phase], 1).T
+
+
+def fourier_mmd_literal(xy_true: torch.Tensor, xy_pred: torch.Tensor, wz: torch.Tensor, k: int) -> torch.Tensor:
+    """Loss.py:39-56 with the random matrix wz [d+1, 7k] supplied by the caller."""
+    N = xy_pred.shape[0]
+
+    def f1(x):                                                   # Loss.py:39-45
+        ones = torch.ones((N, 1), dtype=x.dtype)
+        return torch.cos(torch.cat([x, ones], 1) @ wz)
+
+    e1 = float(np.sqrt(2.0 / k)) * f1(xy_true).mean(0)           # Loss.py:53
+    e2 = float(np.sqrt(2.0 / k)) * f1(xy_pred).mean(0)           # Loss.py:54
+    return ((e1 - e2) ** 2).sum()                                # Loss.py:56

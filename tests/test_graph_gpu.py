@@ -158,3 +158,34 @@ def test_run_graph_determinism_subsets_and_limits(engine):
         engine.run_graph(data, plans, n_runs=1, h_layer_dim=33)
     with pytest.raises(EngineError):
         engine.run_graph(np.zeros((1600, n_var), np.float32), plans, n_runs=1)
+
+
+def test_generate_matches_oracle_and_fits(engine):
+    """CGNN_tf.generate (CGNN.py:155-160): forward sample of a fitted model."""
+    import pandas as pd
+    import cgnn_b200 as cgnn
+    from cgnn_b200 import runtime
+    from cgnn_b200.plan import build_plan, n_params
+    from oracle import cgnn as oc
+    n_var, h, n = 5, 8, 150
+    g = random_dag(n_var, 2, 12)
+    plan = build_plan(g)
+    rng = np.random.default_rng(0)
+    theta = (0.3 * rng.normal(size=n_params(plan, h))).astype(np.float32)
+    noise = rng.normal(size=(plan["n_noise"], n)).astype(np.float32)
+    got = engine.graph_generate(plan, theta, noise, h_layer_dim=h)
+    want = oc.generate(theta.astype(np.float64), noise.astype(np.float64), oc.build_plan(g), h)
+    assert relerr(got, want) < TOL
+    # public API: fit then sample; a trained model's sample must be much closer (in MMD) to the data than an
+    # untrained model's
+    data = pd.DataFrame(make_data(300, n_var, 5), columns=plan["list_nodes"])
+    try:
+        sample = cgnn.CGNN().generate(data, g, h_layer_dim=10, train_epochs=300, test_epochs=1)
+        raw = cgnn.CGNN().generate(data, g, h_layer_dim=10, train_epochs=0, test_epochs=1)
+    finally:
+        runtime.close_engines()
+    assert list(sample.columns) == [c for c in data.columns] and sample.shape == data.shape
+    from oracle import mmd
+    d = data.values.astype(np.float64)
+    d = (d - d.mean(0)) / d.std(0)
+    assert mmd.mmd_loss_blocks(d, sample.values) < 0.3 * mmd.mmd_loss_blocks(d, raw.values)

@@ -174,3 +174,62 @@ def test_limits_and_errors(engine):
         engine.run_pairwise(xy, n_runs=1, exp_policy=7)
     # still usable afterwards
     assert np.all(np.isfinite(engine.run_pairwise(xy, n_runs=1, train_epochs=2, test_epochs=1)["scores"]))
+
+
+# ---- random-feature ("Fourier") MMD: SETTINGS.use_Fast_MMD, Loss.py:35-56 -------------------------------
+# fp32 noise floor of this loss: the frequencies reach 2*gamma*|N(0,1)| ~ 300, so the fp32 rounding of a
+# generated value (6e-8 relative) already moves cos()'s argument by ~2e-5 rad; the reference's own fp32
+# graph sits at the same level.  Bound used here: 2e-4 relative (loss, gradients) against the fp64 oracle.
+FTOL = 2e-4
+
+
+def _rp(k, rng):
+    from oracle.mmd import rp_literal
+    return rp_literal(k, 2, rng).astype(np.float32)
+
+
+@pytest.mark.parametrize("n,h,k", [(200, 12, 10), (1500, 30, 100), (65, 5, 3)])
+def test_fourier_step_debug_matches_oracle(engine, n, h, k):
+    from oracle import gnn as og
+    from oracle.adam import TFAdam
+    rng = np.random.RandomState(n)
+    xy = make_pair(n, n + 1, kind=0)
+    steps = 3
+    theta0 = (0.05 * rng.standard_normal(4 * h + 1)).astype(np.float32)
+    noise = rng.standard_normal((steps, n)).astype(np.float32)
+    wz = np.stack([_rp(k, rng) for _ in range(steps)])
+    got = engine.pairwise_step_debug(xy, noise, theta0, fourier_wz=wz, h_layer_dim=h, use_Fast_MMD=True, nb_vectors_approx_MMD=k)
+    theta = theta0.astype(np.float64)
+    opt = TFAdam(theta.size, 0.01)
+    for s in range(steps):
+        th = theta0 if s == 0 else got["params"][s - 1]            # re-anchor: compare step by step
+        r = og.step_debug(th.astype(np.float64), xy.astype(np.float64), noise[s].astype(np.float64), h,
+                          wz=wz[s].astype(np.float64), k=k)
+        assert abs(got["loss"][s] - r["loss"]) <= FTOL * abs(r["loss"]), (s, got["loss"][s], r["loss"])
+        assert relerr(got["dldy"][s], r["dloss_dout"]) < FTOL
+        assert relerr(got["grad"][s], r["grad"]) < FTOL
+
+
+def test_fourier_fixture_from_reference_code(engine):
+    """GNN_tf(use_Fast_MMD=True) of the reference, executed over the TF-1 shim (oracle/make_golden.py)."""
+    import os
+    z = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "ref_shim_pairwise.npz"))
+    data, h, tr, te, k = z["f_data"], int(z["f_h"]), int(z["f_train"]), int(z["f_test"]), int(z["f_k"])
+    got = engine.pairwise_step_debug(data, z["f_noise"][:tr].astype(np.float32), z["f_theta0"].astype(np.float32),
+                                     fourier_wz=z["f_wz"][:tr].astype(np.float32), h_layer_dim=h, use_Fast_MMD=True,
+                                     nb_vectors_approx_MMD=k)
+    assert relerr(got["loss"], z["f_losses"][:tr]) < 5 * FTOL          # includes 9 steps of trajectory drift
+
+
+def test_fourier_run_is_deterministic_and_trains(engine):
+    xy = np.stack([make_pair(400, 5, 0), make_pair(400, 6, 1)])
+    kw = dict(n_runs=2, h_layer_dim=20, train_epochs=150, test_epochs=20, seed=3, use_Fast_MMD=True, nb_vectors_approx_MMD=100,
+              want_trace=True)
+    a = engine.run_pairwise(xy, **kw)
+    b = engine.run_pairwise(xy, **kw)
+    assert np.array_equal(a["scores"], b["scores"]) and np.all(np.isfinite(a["scores"])) and np.all(a["scores"] > 0)
+    tr = a["trace"][:, :150]
+    assert np.all(tr[:, -20:].mean(1) < 0.5 * tr[:, :5].mean(1)), "the random-feature loss should go down"
+    from cgnn_b200 import EngineError
+    with pytest.raises(EngineError):
+        engine.run_pairwise(xy, n_runs=1, use_Fast_MMD=True, nb_vectors_approx_MMD=1000)
