@@ -272,7 +272,6 @@ int cgnn_b200_pairwise_step_debug(cgnn_ctx* ctx, const cgnn_hparams* hp, const f
                                   float* out_yhat, float* out_dldy, float* out_grad, float* out_params) {
     if (!ctx) return CGNN_ERR_ARG;
     if (!hp) return fail(ctx, CGNN_ERR_ARG, "hparams is NULL");
-    if (!noise || !init_params) return fail(ctx, CGNN_ERR_ARG, "step_debug needs caller-supplied noise and parameters");
     if (n_steps < 1) return fail(ctx, CGNN_ERR_ARG, "n_steps must be >= 1");
     cgnn_hparams h2 = *hp;
     h2.train_epochs = n_steps;

@@ -135,19 +135,23 @@ class Engine:
         self._check(rc, "cgnn_b200_run_pairwise")
         return dict(scores=scores, trace=trace, params=pout)
 
-    def pairwise_step_debug(self, xy, noise, init_params, fourier_wz=None, **kw):
+    def pairwise_step_debug(self, xy, noise, init_params, fourier_wz=None, n_steps=None, **kw):
         """Parity probe: consecutive train steps of ONE instance (column 0 = cause).
         fourier_wz [n_steps, 3, 7k]: with use_Fast_MMD=True, the random matrix of Loss.py:35-37 per step."""
         hp = make_hparams(**kw)
         if fourier_wz is not None:
             fourier_wz = np.ascontiguousarray(fourier_wz, np.float32)
-            assert fourier_wz.shape == (noise.shape[0], 3, 7 * hp.fast_mmd_vectors)
+            assert fourier_wz.shape[1:] == (3, 7 * hp.fast_mmd_vectors)
         xy = np.ascontiguousarray(xy, np.float32)
-        noise = np.ascontiguousarray(noise, np.float32)
-        init_params = np.ascontiguousarray(init_params, np.float32)
-        n_rows, n_steps = xy.shape[0], noise.shape[0]
+        n_rows = xy.shape[0]
         P = 4 * hp.h_layer_dim + 1
-        assert noise.shape == (n_steps, n_rows) and init_params.shape == (P,)
+        if noise is not None:                    # None: the kernel's own Philox noise (stream uid 0)
+            noise = np.ascontiguousarray(noise, np.float32)
+            n_steps = noise.shape[0]
+            assert noise.shape == (n_steps, n_rows)
+        if init_params is not None:
+            init_params = np.ascontiguousarray(init_params, np.float32)
+            assert init_params.shape == (P,)
         out = dict(loss=np.empty(n_steps, np.float32), yhat=np.empty((n_steps, n_rows), np.float32),
                    dldy=np.empty((n_steps, n_rows), np.float32), grad=np.empty((n_steps, P), np.float32),
                    params=np.empty((n_steps, P), np.float32))

@@ -50,7 +50,7 @@ class GraphScorer(object):
     model), CGNN.py:217 / CGNN_confounders.py:236-237."""
 
     def __init__(self, df_data, confounders=False, **kwargs):
-        self.kwargs = {k: v for k, v in kwargs.items() if k not in ("nb_runs", "nb_jobs")}
+        self.kwargs = {k: v for k, v in kwargs.items() if k not in ("nb_runs", "nb_jobs", "speculation_horizon")}
         self.nb_runs = int(kwargs.get("nb_runs", SETTINGS.NB_RUNS))
         self.confounders = confounders
         self.df = df_data
@@ -59,6 +59,7 @@ class GraphScorer(object):
         self.cache = {}
         self.pending = None          # list of graphs while speculating
         self.batches = []            # sizes of the engine batches (diagnostics)
+        self.horizon = int(kwargs.get("speculation_horizon", 0)) or None
 
     def _bind(self, graph):
         nodes = set(graph.skeleton.get_list_nodes() if self.confounders else graph.get_list_nodes())
@@ -81,8 +82,22 @@ class GraphScorer(object):
         if key in self.cache:                    # speculating, but this one is already known
             return self.cache[key] + self.penalty(graph)
         if all(structure_key(g) != key for g in self.pending):
+            if len(self.pending) >= self._horizon():
+                raise _Speculating()     # enough candidates to fill the GPUs: score them before guessing further
             self.pending.append(deepcopy(graph))
         return float("nan")
+
+    def _horizon(self):
+        """How many unseen candidates one speculative batch may hold: enough instances for two full waves
+        of the graph kernel (one CTA per SM) on every GPU of the job.  A larger batch is no faster per
+        candidate, and everything speculated after an accepted move is wasted."""
+        if self.horizon is None:
+            try:
+                slots = sum(e.device_info()["n_sm"] for e in runtime.get_engines()) * runtime.dist_info()[1]
+            except Exception:
+                slots = 148
+            self.horizon = max(1, (2 * slots) // max(1, self.nb_runs))
+        return self.horizon
 
     def end_of_sweep(self):
         if self.pending is not None:

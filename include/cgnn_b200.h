@@ -119,7 +119,7 @@ int  cgnn_b200_run_pairwise(cgnn_ctx* ctx, const cgnn_hparams* hp,
  * with caller-supplied parameters and noise, dumping what the reference's graph would hold at
  * each sess.run (GNN.py:93-96): the loss before the update, the generated column, dLoss/d out_y,
  * the parameter gradient and the parameters after the Adam update.  Runs the production kernel.
- *   xy [n_rows][2], noise [n_steps][n_rows], init_params [4h+1]
+ *   xy [n_rows][2], noise [n_steps][n_rows] or NULL (in-kernel Philox, stream uid 0), init_params [4h+1] or NULL
  *   fourier_wz  NULL, or - with hp->fast_mmd_vectors = k - the random matrix of Loss.py:35-37 for every step,
  *               [n_steps][3][7k] (rows: frequency on the cause, frequency on the effect, phase)
  *   out_loss [n_steps], out_yhat [n_steps][n_rows], out_dldy [n_steps][n_rows],

@@ -33,6 +33,9 @@ class FakeEngine(object):
     def close(self):
         pass
 
+    def device_info(self):
+        return dict(n_sm=8, ctas_per_sm_pairwise=2)
+
     def run_pairwise(self, xy, n_rows=None, n_runs=1, uid_base=0, **kw):
         xy = np.asarray(xy)
         self.calls.append(("pairwise", xy.shape[0], n_runs, int(uid_base)))

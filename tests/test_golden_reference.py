@@ -68,3 +68,33 @@ def test_graph_and_confounder_models():
         score, ev = oc.evaluate(theta, data, z["noise"][tr:], plan, h)
         np.testing.assert_allclose(np.concatenate([losses, ev]), z["losses"], rtol=TIGHT)
         assert abs(score - float(z["score"])) < TIGHT * score
+
+
+def test_fourier_loss_and_fast_mmd_generator():
+    """Fourier_MMD_Loss_tf (Loss.py:35-56) and GNN_tf(use_Fast_MMD=True) of the reference, with the random
+    matrix its rp() drew: the oracle's restatement gives the same numbers."""
+    import torch
+    from oracle import mmd, gnn
+    z = np.load(os.path.join(GOLD, "ref_shim_mmd.npz"))
+    for k in range(2):
+        v = float(mmd.fourier_mmd_literal(torch.tensor(z["ft%d" % k]), torch.tensor(z["fp%d" % k]), torch.tensor(z["fwz%d" % k]),
+                                          int(z["fk%d" % k])))
+        assert abs(v - float(z["floss%d" % k])) < 1e-12 * v
+    z = np.load(os.path.join(GOLD, "ref_shim_pairwise.npz"))
+    tr, k, h = int(z["f_train"]), int(z["f_k"]), int(z["f_h"])
+    data = z["f_data"].astype(np.float64)
+    theta, losses, _ = gnn.train(z["f_theta0"], data, z["f_noise"][:tr], h, wz=z["f_wz"][:tr], k=k)
+    score, ev = gnn.evaluate(theta, data, z["f_noise"][tr:], h, wz=z["f_wz"][tr:], k=k)
+    np.testing.assert_allclose(np.concatenate([losses, ev]), z["f_losses"], rtol=TIGHT)
+    assert abs(score - float(z["f_score"])) < TIGHT * score
+
+
+def test_rp_literal_shape_and_scales():
+    from oracle.mmd import rp_literal
+    from oracle import GAMMAS
+    wz = rp_literal(500, 3, np.random.RandomState(0))
+    assert wz.shape == (4, 3500)
+    for g, gam in enumerate(GAMMAS):
+        blk = wz[:3, 500 * g:500 * (g + 1)]
+        assert abs(blk.std() / (2 * gam) - 1) < 0.1
+    assert 0 <= wz[3].min() and wz[3].max() <= 2 * np.pi

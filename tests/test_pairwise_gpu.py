@@ -233,3 +233,28 @@ def test_fourier_run_is_deterministic_and_trains(engine):
     from cgnn_b200 import EngineError
     with pytest.raises(EngineError):
         engine.run_pairwise(xy, n_runs=1, use_Fast_MMD=True, nb_vectors_approx_MMD=1000)
+
+
+def test_in_kernel_random_streams(engine):
+    """The kernel's Philox noise and initial parameters against the numpy restatement (tests/philox_np.py),
+    and their first two moments."""
+    import philox_np
+    n, seed = 1500, 0x1234567890
+    xy = make_pair(n, 3, 0)
+    # a 2-unit generator that copies its noise input: yhat = relu(e) - relu(-e) = e
+    theta = np.array([0, 0, 1, -1, 0, 0, 1, -1, 0], np.float32)
+    got = engine.pairwise_step_debug(xy, None, theta, n_steps=3, h_layer_dim=2, learning_rate=0.0, seed=seed)
+    for s in range(3):
+        want = philox_np.pairwise_noise(seed, 0, s, n)
+        np.testing.assert_allclose(got["yhat"][s], want, rtol=2e-5, atol=2e-6)
+    e = got["yhat"].ravel()
+    assert abs(e.mean()) < 0.05 and abs(e.std() - 1) < 0.05 and abs(np.mean(e ** 3)) < 0.1
+    assert abs(np.corrcoef(got["yhat"][0], got["yhat"][1])[0, 1]) < 0.08
+    # initial parameters N(0, init_std^2), biases included (GNN.py:21-29)
+    r = engine.run_pairwise(xy[None], n_runs=1, train_epochs=0, test_epochs=1, h_layer_dim=30, seed=seed,
+                            init_std=0.05, want_params=True)
+    for d in range(2):
+        np.testing.assert_allclose(r["params"][d], philox_np.init_params(seed, d, 121, 0.05), rtol=2e-5, atol=1e-7)
+    big = engine.run_pairwise(np.repeat(xy[None], 8, 0), n_runs=8, train_epochs=0, test_epochs=1, h_layer_dim=64,
+                              want_params=True)["params"]
+    assert abs(big.mean()) < 2e-3 and abs(big.std() - 0.05) < 2e-3

@@ -1,0 +1,83 @@
+"""Runs the three bundled examples (BASELINE configs[0..2]) at the reference's own settings through the
+public API and scores the decisions against the bundled ground truth.  Writes profiles/r1_examples_full.json.
+Usage: python tools/run_examples.py [--runs 32] [--train 1000] [--test 500] [--seeds 1]"""
+import argparse, json, os, sys, time
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import numpy as np
+import pandas as pd
+import cgnn
+from cgnn.utils import CCEPC_PairsFileReader as CC
+from cgnn_b200.CGNN import hill_climbing
+from cgnn_b200.CGNN_confounders import hill_climbing_confounders
+from cgnn_b200.utils.scaling import scale
+from sklearn.metrics import average_precision_score
+
+ap = argparse.ArgumentParser()
+ap.add_argument("--runs", type=int, default=32)
+ap.add_argument("--train", type=int, default=1000)
+ap.add_argument("--test", type=int, default=500)
+ap.add_argument("--seeds", type=int, default=1)
+ap.add_argument("--out", default="profiles/r1_examples_full.json")
+a = ap.parse_args()
+EX = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "examples")
+S = cgnn.SETTINGS
+S.verbose = False
+S.NB_RUNS, S.train_epochs, S.test_epochs = a.runs, a.train, a.test
+res = dict(settings=dict(nb_runs=a.runs, train_epochs=a.train, test_epochs=a.test, exp_policy=S.exp_policy), seeds=[])
+
+
+def edge_aupr(graph, truth, skeleton_edges):
+    """AUPR over the two orientations of every skeleton edge, score = edge weight if present else 0."""
+    w = {(x, y): float(s) for x, y, s in graph.get_list_edges()}
+    ys, ss = [], []
+    for x, y in skeleton_edges:
+        for e in ((x, y), (y, x)):
+            ys.append(1 if e in truth else 0)
+            ss.append(w.get(e, 0.0))
+    return float(average_precision_score(ys, ss))
+
+
+for seed in range(a.seeds):
+    S.seed = seed
+    r = dict(seed=seed)
+    # ---- config 1: pairwise
+    t0 = time.time()
+    S.h_layer_dim = 30
+    data = CC(os.path.join(EX, "Example_pairwise_pairs.csv"), scale=True)
+    pred = cgnn.GNN(backend="TensorFlow").predict_dataset(data)
+    target = pd.read_csv(os.path.join(EX, "Example_pairwise_targets.csv"))["Target"].values
+    r["pairwise"] = dict(predictions=[float(p) for p in pred], targets=target.tolist(),
+                         correct=int(np.sum(np.sign(pred) == target)), seconds=time.time() - t0)
+    # ---- config 2: graph
+    S.h_layer_dim = 20
+    t0 = time.time()
+    df = pd.read_csv(os.path.join(EX, "Example_graph_numdata.csv"))
+    umg = cgnn.UndirectedGraph(pd.read_csv(os.path.join(EX, "Example_graph_skeleton.csv")))
+    truth = {tuple(x) for x in pd.read_csv(os.path.join(EX, "Example_graph_target.csv")).values.tolist()}
+    dag = cgnn.GNN(backend="TensorFlow").orient_graph(df, umg)
+    pw_hits = sum((x, y) in truth for x, y, _ in dag.get_list_edges())
+    pw_aupr = edge_aupr(dag, truth, umg.get_list_edges_without_duplicate())
+    t1 = time.time()
+    out = cgnn.CGNN(backend="TensorFlow").orient_directed_graph(df, dag)
+    r["graph"] = dict(pairwise_correct=int(pw_hits), pairwise_aupr=pw_aupr,
+                      cgnn_correct=int(sum((x, y) in truth for x, y, _ in out.get_list_edges())), n_edges=30,
+                      cgnn_aupr=edge_aupr(out, truth, umg.get_list_edges_without_duplicate()), acyclic=not out.is_cyclic(),
+                      batches=list(hill_climbing.last_batches), seconds_pairwise=t1 - t0, seconds_cgnn=time.time() - t1)
+    # ---- config 3: hidden variables
+    t0 = time.time()
+    df = pd.read_csv(os.path.join(EX, "Example_graph_confounders_numdata.csv"))
+    df = pd.DataFrame(scale(df.values), columns=df.columns)
+    skel = cgnn.UndirectedGraph(pd.read_csv(os.path.join(EX, "Example_graph_confounders_skeleton.csv")))
+    truth = {tuple(x) for x in pd.read_csv(os.path.join(EX, "Example_graph_confounders_target.csv")).values.tolist()}
+    dag = cgnn.GNN(backend="TensorFlow").orient_graph_confounders(df, skel)
+    t1 = time.time()
+    out = cgnn.CGNN_confounders(backend="TensorFlow").orient_directed_graph(df, dag)
+    found = {(x, y) for x, y, _ in out.get_list_edges()}
+    spurious = {frozenset(e) for e in (("V11", "V9"), ("V12", "V14"), ("V17", "V19"))}
+    r["confounders"] = dict(n_edges=len(found), true_positive=len(found & truth), n_truth=len(truth),
+                            spurious_links_removed=int(sum(frozenset(e) not in {frozenset(f) for f in found} for e in spurious)),
+                            acyclic=not out.is_cyclic(), batches=list(hill_climbing_confounders.last_batches),
+                            seconds_pairwise=t1 - t0, seconds_cgnn=time.time() - t1)
+    res["seeds"].append(r)
+    print(json.dumps(r))
+json.dump(res, open(a.out, "w"), indent=1)
