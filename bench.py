@@ -129,6 +129,54 @@ def run_reference(args, rank, world):
     }))
 
 
+def graph_leg(eng, pol, train=60, test=30):
+    """Secondary numbers (not the headline metric): the graph instance kernel on this rank's GPU.
+    C2 = bundled 22-variable example, the start DAG + its 27 acyclic single reversals x 32 runs (one converged
+    hill-climbing sweep, 896 instances, N=500); C5 = synthetic 20-variable DAG, N=1500 after subsampling, 16 runs."""
+    from copy import deepcopy
+    import pandas as pd
+    from cgnn_b200 import synth, DirectedGraph
+    from cgnn_b200.plan import build_plan
+    from cgnn_b200.utils.scaling import scale
+    ex = os.path.join(ROOT, "examples")
+
+    def cands(dag, limit=None):
+        out = [dag]
+        for a, b, _ in dag.get_list_edges():
+            t = deepcopy(dag)
+            t.reverse_edge(a, b)
+            if not t.is_cyclic():
+                out.append(t)
+        return out[:limit]
+
+    def one(df, graphs, n_runs, subsets, n):
+        plans = [build_plan(g, columns=list(df.columns)) for g in graphs]
+        X = scale(df.values).astype(np.float32)
+        kw = dict(h_layer_dim=20, train_epochs=train, test_epochs=test, exp_policy=pol, seed=1)
+        eng.run_graph(X, plans[:1], n_runs=2, row_subsets=None if subsets is None else subsets[:2], **kw)
+        eng.run_graph(X, plans, n_runs=n_runs, row_subsets=subsets, **kw)
+        ms = eng.last_kernel_ms
+        n_inst, d = len(plans) * n_runs, X.shape[1]
+        P = n * n + n * (n - 1) // 2
+        flops = n_inst * (train * (n * n * (5 * d + 28) + (n * (n - 1) // 2) * (7 * d + 28)) + test * (3 * d + 14) * P)
+        return {"instances": n_inst, "rows": n, "vars": d, "steps": [train, test], "kernel_ms": ms,
+                "train_steps_per_s": n_inst * train / (ms * 1e-3), "algorithmic_tflops": flops / (ms * 1e-3) / 1e12}
+
+    df = pd.read_csv(os.path.join(ex, "Example_graph_numdata.csv"))
+    dag = DirectedGraph(pd.read_csv(os.path.join(ex, "Example_graph_target.csv")))
+    res = {"C2_bundled_graph_sweep": one(df, cands(dag), 32, None, 500)}
+    X, edges = synth.make_dag_dataset(20, 2000, 3)
+    df5 = pd.DataFrame(X, columns=["V%d" % k for k in range(20)])
+    g = DirectedGraph()
+    for a, b in edges:
+        g.add("V%d" % a, "V%d" % b, 1.0)
+    c5 = cands(g, 10)
+    subs = np.stack([np.random.default_rng(k).permutation(2000)[:1500] for k in range(len(c5) * 16)]).astype(np.int32)
+    res["C5_synthetic_20var"] = one(df5, c5, 16, subs, 1500)
+    res["note"] = "FP32-pipe bound kernel; algorithmic flops per SURVEY 8(d) (PP counted once per unordered pair)"
+    return res
+
+
 def workload_config(args, world):
     return {"workload": "synthetic pairwise sweep slice (BASELINE configs[3]): %d pairs/GPU/step x nb_runs=%d x 2 "
                         "directions, n=%d rows, h=%d, %d train + %d eval steps per instance"
@@ -153,6 +201,7 @@ def main():
     ap.add_argument("--train", type=int, default=TRAIN)
     ap.add_argument("--test", type=int, default=TEST)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-graph", action="store_true", help="skip the secondary graph-kernel measurements")
     args = ap.parse_args()
     TRAIN, TEST = args.train, args.test
 
@@ -292,6 +341,8 @@ def main():
                    "pair_scores_per_s": world * args.pairs * args.steps / e2e_s,
                    "api": "cgnn_b200.GNN.predict_dataset(DataFrame of numpy pairs)"},
            "gpu_launches": launches, "clocks": clocks, "roofline": roof}
+    if not args.no_graph and rank == 0:
+        out["graph_configs"] = graph_leg(eng, args.exp_policy)          # secondary: BASELINE configs[1] / [4] shapes
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         v, r, sample = cpu_baseline_sample(4, 2)
         out["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": r["cores"], "kind": "port", "sample": sample}
