@@ -125,6 +125,8 @@ int cgnn_b200_set_stream(cgnn_ctx* ctx, void* stream) {
 float cgnn_b200_last_kernel_ms(const cgnn_ctx* ctx) { return ctx ? ctx->last_ms : -1.f; }
 int cgnn_b200_last_launch_count(const cgnn_ctx* ctx) { return ctx ? ctx->last_launches : 0; }
 
+int cgnn_b200_last_graph_cluster(const cgnn_ctx* ctx) { return ctx ? ctx->last_cluster : 0; }
+
 int cgnn_b200_device_info(const cgnn_ctx* ctx, int* n_sm, int* ctas_per_sm_pairwise) {
     if (!ctx) return CGNN_ERR_ARG;
     if (n_sm) *n_sm = ctx->prop.multiProcessorCount;

@@ -300,9 +300,11 @@ __device__ __forceinline__ float warp_reduce32(float (&v)[32], int lane) {
 // TF-1 Adam, fp32, one parameter per call.  lr_t = lr*sqrt(1-b2^t)/(1-b1^t) is computed by the caller.
 // ---------------------------------------------------------------------------------------------
 __device__ __forceinline__ float adam_update(float theta, float g, float& m, float& v, float lr_t) {
-    m = 0.9f * m + 0.1f * g;                         // (1-beta1) rounds to 0.1f in fp32 as in TF
-    v = 0.999f * v + 0.001f * g * g;
-    return theta - lr_t * m / (sqrtf(v) + 1e-8f);
+    // explicit rounding intrinsics: no FMA contraction choices left to the compiler, so every code path that
+    // calls this (pairwise / graph kernel, single CTA / cluster) produces the same bits from the same inputs
+    m = __fmaf_rn(0.9f, m, __fmul_rn(0.1f, g));                     // (1-beta1) rounds to 0.1f in fp32 as in TF
+    v = __fmaf_rn(0.999f, v, __fmul_rn(0.001f, __fmul_rn(g, g)));
+    return __fsub_rn(theta, __fdiv_rn(__fmul_rn(lr_t, m), __fadd_rn(__fsqrt_rn(v), 1e-8f)));
 }
 
 }  // namespace cgnn

@@ -20,12 +20,22 @@
 // MLP backward pass - dLoss/dPred is never written to memory.  Column j (DP floats) arrives as
 // DP/4 128-bit broadcast loads.  Parameter gradients are reduced across the 32 rows of a block with
 // the transposing warp reduction and accumulated across warps with fixed-point shared atomics.
+//
+// Thread-block clusters: when a batch has fewer instances than the GPU has SMs (a hill-climbing tail, the
+// 20-variable configuration on 8 GPUs) one instance is given a CLUSTER of 2-4 CTAs.  Every CTA keeps the whole
+// generated matrix and all parameters (the generator forward is replicated - ~3 % of a step), the row blocks of
+// the MMD / backward pass are split over the CTAs, and once per step the fixed-point gradient accumulators are
+// summed across the cluster through distributed shared memory, so all CTAs apply the same Adam update.
 #pragma once
+#include <cooperative_groups.h>
 #include "common.cuh"
 
 namespace cgnn {
 
+namespace cg = cooperative_groups;
+
 constexpr int GR_NT = 512;
+constexpr int GR_MAX_CLUSTER = 8;
 constexpr int GR_NW = GR_NT / 32;
 constexpr int GR_MAX_VAR = 32;
 constexpr int GR_MAX_H = 32;
@@ -84,7 +94,7 @@ __host__ __device__ inline size_t gr_smem_bytes(int NP, int DP, int n_noise, int
     const int pp = (p_max + 3) & ~3;
     size_t b = 0;
     b += size_t(pp) * 8;                          // g64
-    b += size_t(GR_NW + 4) * 8;                   // red, TT, beta powers, lr_t
+    b += size_t(GR_NW + 4 + GR_MAX_CLUSTER) * 8;  // red, TT, beta powers, lr_t, per-CTA partials of a cluster
     b += size_t(NP) * DP * 4;                     // Pm
     b += size_t(GR_NW) * nn_pad * 32 * 4;         // nbuf
     b += size_t(pp) * 4 * 3;                      // theta, m, v
@@ -305,6 +315,21 @@ __device__ __forceinline__ double gr_block_sum(double v, double* red, int warp, 
     return t;
 }
 
+// Sum of one double per CTA over the cluster (fixed order: deterministic); result valid in thread 0 of every CTA.
+__device__ __forceinline__ double gr_cluster_sum(double v, double* red, int warp, int lane, cg::cluster_group& cl,
+                                                 int csz, int crank) {
+    double t = gr_block_sum(v, red, warp, lane);
+    if (csz == 1) return t;
+    if (warp == 0 && lane == 0)
+        for (int r = 0; r < csz; ++r) cl.map_shared_rank(red, r)[GR_NW + 4 + crank] = t;
+    cl.sync();
+    double tot = 0.0;
+    if (warp == 0 && lane == 0)
+        for (int r = 0; r < csz; ++r) tot += red[GR_NW + 4 + r];
+    cl.sync();
+    return tot;
+}
+
 template <int DP, int HP, int POL>
 __global__ void __launch_bounds__(GR_NT, 1) graph_kernel(const GraphArgs a) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -312,13 +337,16 @@ __global__ void __launch_bounds__(GR_NT, 1) graph_kernel(const GraphArgs a) {
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const int h = a.h, N = a.N, NB = (N + 31) >> 5;
     const int pp = (a.p_max + 3) & ~3;
+    cg::cluster_group cl = cg::this_cluster();
+    const int csz = int(cl.num_blocks()), crank = int(cl.block_rank());
+    const int rb0 = crank + csz * warp, rbs = csz * GR_NW;        // this warp's row blocks of the MMD passes
 
     GrSmem s;
     {
         unsigned char* p = smem_raw;
         s.nn_pad = (a.n_noise + 3) & ~3;
         s.g64 = reinterpret_cast<long long*>(p);   p += size_t(pp) * 8;
-        s.red = reinterpret_cast<double*>(p);      p += size_t(GR_NW + 4) * 8;
+        s.red = reinterpret_cast<double*>(p);      p += size_t(GR_NW + 4 + GR_MAX_CLUSTER) * 8;
         s.Pm = reinterpret_cast<float*>(p);        p += size_t(a.NP) * DP * 4;
         s.nbuf = reinterpret_cast<float*>(p);      p += size_t(GR_NW) * s.nn_pad * 32 * 4;
         s.theta = reinterpret_cast<float*>(p);     p += size_t(pp) * 4;
@@ -332,9 +360,18 @@ __global__ void __launch_bounds__(GR_NT, 1) graph_kernel(const GraphArgs a) {
     const double invN2 = 1.0 / (double(N) * double(N));
 
     for (;;) {
-        __syncthreads();
-        if (tid == 0) s_inst = atomicAdd(a.counter, 1);
-        __syncthreads();
+        if (csz > 1) {     // CTA 0 of the cluster pulls the next instance and tells its peers
+            cl.sync();
+            if (crank == 0 && tid == 0) {
+                const int v = atomicAdd(a.counter, 1);
+                for (int r = 0; r < csz; ++r) *cl.map_shared_rank(&s_inst, r) = v;
+            }
+            cl.sync();
+        } else {
+            __syncthreads();
+            if (tid == 0) s_inst = atomicAdd(a.counter, 1);
+            __syncthreads();
+        }
         if (s_inst >= a.n_inst) break;
         const int2 inst = a.inst[s_inst];
         const int out = inst.y;
@@ -369,7 +406,7 @@ __global__ void __launch_bounds__(GR_NT, 1) graph_kernel(const GraphArgs a) {
         // ---- TT (constant per instance) -------------------------------------------------------
         {
             double part = 0.0;
-            for (int rb = warp; rb < NB; rb += GR_NW) {
+            for (int rb = rb0; rb < NB; rb += rbs) {
                 const int i = 32 * rb + lane;
                 float pf[DP];
                 float2 p[DP / 2];
@@ -379,7 +416,7 @@ __global__ void __launch_bounds__(GR_NT, 1) graph_kernel(const GraphArgs a) {
                 const double v = gr_mmd_eval_row<DP, POL, true>(T, N, p);
                 if (i < N) part += v;
             }
-            const double tt = gr_block_sum(part, s.red, warp, lane);
+            const double tt = gr_cluster_sum(part, s.red, warp, lane, cl, csz, crank);
             if (tid == 0) s.red[GR_NW] = tt;
         }
 
@@ -410,7 +447,7 @@ __global__ void __launch_bounds__(GR_NT, 1) graph_kernel(const GraphArgs a) {
             const bool want_loss = !train || a.dbg_loss || (a.trace && a.trace_every > 0 && it % a.trace_every == 0);
             if (want_loss) {
                 double part = 0.0;
-                for (int rb = warp; rb < NB; rb += GR_NW) {
+                for (int rb = rb0; rb < NB; rb += rbs) {
                     const int i = 32 * rb + lane;
                     float pf[DP];
                     float2 p[DP / 2];
@@ -420,19 +457,19 @@ __global__ void __launch_bounds__(GR_NT, 1) graph_kernel(const GraphArgs a) {
                     const double v = gr_mmd_eval_row<DP, POL, false>(s.Pm, N, p) - 2.0 * gr_mmd_eval_row<DP, POL, true>(T, N, p);
                     if (i < N) part += v;
                 }
-                const double sum = gr_block_sum(part, s.red, warp, lane);
+                const double sum = gr_cluster_sum(part, s.red, warp, lane, cl, csz, crank);
                 if (tid == 0) {
                     const float loss = float((sum + s.red[GR_NW]) * invN2);
                     if (!train) score_sum += double(loss);
-                    if (a.trace) a.trace[size_t(out) * epochs + it] = loss;
+                    if (a.trace && crank == 0) a.trace[size_t(out) * epochs + it] = loss;
                     if (a.dbg_loss && train) a.dbg_loss[it] = loss;
                 }
-            } else if (a.trace && tid == 0) {
+            } else if (a.trace && tid == 0 && crank == 0) {
                 a.trace[size_t(out) * epochs + it] = __int_as_float(0x7fc00000);
             }
             if (!train) continue;
             // ---- MMD gradient + generator backward, row block by row block ------------------------
-            for (int rb = warp; rb < NB; rb += GR_NW) {
+            for (int rb = rb0; rb < NB; rb += rbs) {
                 const int i = 32 * rb + lane;
                 float gl[DP];
                 {
@@ -454,9 +491,24 @@ __global__ void __launch_bounds__(GR_NT, 1) graph_kernel(const GraphArgs a) {
                 gr_backward_block<DP, HP>(s, nb, i, lane, gl);
                 __syncwarp();
             }
-            __syncthreads();
             // ---- Adam --------------------------------------------------------------------------
-            {
+            if (csz > 1) {
+                // every CTA sums the fixed-point accumulators of the whole cluster (integer: exact, order-free)
+                // and applies the same update to its own copy of the parameters
+                cl.sync();
+                const float lr_t = float(s.red[GR_NW + 3]);
+                for (int q = tid; q < PPAD; q += GR_NT) {
+                    long long tot = 0;
+                    for (int r = 0; r < csz; ++r) tot += cl.map_shared_rank(s.g64, r)[q];
+                    const float g = float(double(tot) * CGNN_FX_INV);
+                    float m = s.am[q], v = s.av[q];
+                    const float th = adam_update(s.theta[q], g, m, v, lr_t);
+                    s.am[q] = m; s.av[q] = v; s.theta[q] = th;
+                }
+                cl.sync();                                   // peers have read this CTA's accumulators
+                for (int q = tid; q < PPAD; q += GR_NT) s.g64[q] = 0;
+            } else {
+                __syncthreads();
                 const float lr_t = float(s.red[GR_NW + 3]);
                 if (a.dbg_grad)
                     for (int q = tid; q < P; q += GR_NT)
@@ -475,12 +527,12 @@ __global__ void __launch_bounds__(GR_NT, 1) graph_kernel(const GraphArgs a) {
                 }
             }
         }
-        if (a.params_out) {            // evaluation does not touch the parameters: these are the trained ones
+        if (a.params_out && crank == 0) {   // evaluation does not touch the parameters: these are the trained ones
             __syncthreads();
             for (int q = tid; q < P; q += GR_NT)
                 a.params_out[size_t(out) * a.ld_params + q] = s.theta[gr_pad_index(*s.desc, q, h, HP)];
         }
-        if (tid == 0 && a.scores) a.scores[out] = a.test_epochs > 0 ? float(score_sum / double(a.test_epochs)) : 0.f;
+        if (tid == 0 && crank == 0 && a.scores) a.scores[out] = a.test_epochs > 0 ? float(score_sum / double(a.test_epochs)) : 0.f;
     }
 }
 

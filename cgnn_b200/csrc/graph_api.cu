@@ -1,4 +1,5 @@
 // C-ABI of the graph path: cgnn_b200_run_graph, cgnn_b200_graph_step_debug.  See include/cgnn_b200.h.
+#include <cmath>
 #include <vector>
 
 #include "ctx.h"
@@ -22,8 +23,8 @@ static __global__ void gather_rows_kernel(const float* __restrict__ data, int n_
 
 
 #define DECL(DP_)                                                                                  \
-    cudaError_t cgnn_launch_graph_dp##DP_##_hp20(int, const GraphArgs&, int, size_t, cudaStream_t); \
-    cudaError_t cgnn_launch_graph_dp##DP_##_hp32(int, const GraphArgs&, int, size_t, cudaStream_t);
+    cudaError_t cgnn_launch_graph_dp##DP_##_hp20(int, const GraphArgs&, int, int, size_t, cudaStream_t, int*); \
+    cudaError_t cgnn_launch_graph_dp##DP_##_hp32(int, const GraphArgs&, int, int, size_t, cudaStream_t, int*);
 DECL(8) DECL(16) DECL(20) DECL(24) DECL(32)
 #undef DECL
 
@@ -34,9 +35,12 @@ static int pick_dp(int n_var) {
     return 0;
 }
 
-static cudaError_t launch_graph(int dp, int hp, int pol, const GraphArgs& a, int grid, size_t smem, cudaStream_t st) {
-#define CASE(DP_) \
-    case DP_: return hp == 20 ? cgnn_launch_graph_dp##DP_##_hp20(pol, a, grid, smem, st) : cgnn_launch_graph_dp##DP_##_hp32(pol, a, grid, smem, st);
+static cudaError_t launch_graph(int dp, int hp, int pol, const GraphArgs& a, int n_clusters, int csz, size_t smem,
+                                cudaStream_t st, int* max_clusters) {
+#define CASE(DP_)                                                                                              \
+    case DP_:                                                                                                  \
+        return hp == 20 ? cgnn_launch_graph_dp##DP_##_hp20(pol, a, n_clusters, csz, smem, st, max_clusters)    \
+                        : cgnn_launch_graph_dp##DP_##_hp32(pol, a, n_clusters, csz, smem, st, max_clusters);
     switch (dp) { CASE(8) CASE(16) CASE(20) CASE(24) CASE(32) }
 #undef CASE
     return cudaErrorInvalidValue;
@@ -208,10 +212,29 @@ static int run_graph_impl(cgnn_ctx* ctx, const cgnn_hparams* hp, const float* da
     if (smem > size_t(ctx->prop.sharedMemPerBlockOptin))
         return fail(ctx, CGNN_ERR_LIMIT, "graph instance needs %zu B of shared memory (rows %d x cols %d, %d noise columns, %d parameters); "
                     "device allows %zu", smem, n_rows, DP, n_noise, p_max, size_t(ctx->prop.sharedMemPerBlockOptin));
-    const int grid = std::min(n_inst, ctx->prop.multiProcessorCount);
+    // ---- CTAs per instance: a cluster when the batch cannot fill the GPU with one CTA per instance ----------
+    const int NB = NP / 32;
+    int best_csz = 1, best_slots = std::max(1, ctx->prop.multiProcessorCount);
+    double best_cost = 1e300;
+    for (int csz = 1; csz <= 4; ++csz) {
+        if (dbg_host && csz > 1) break;                              // the parity probe runs on one CTA
+        if (hp->graph_cluster > 0 && csz != hp->graph_cluster) continue;
+        int slots = 0;
+        if (launch_graph(DP, HP, hp->exp_policy, a, -1, csz, smem, ctx->stream, &slots) != cudaSuccess || slots < 1) {
+            cudaGetLastError();
+            continue;
+        }
+        const int rb_per_cta = (NB + csz - 1) / csz;
+        const double rounds_rows = double((rb_per_cta + GR_NW - 1) / GR_NW);          // row-block rounds per step
+        const double cost = std::ceil(double(n_inst) / slots) * (rounds_rows + 0.1);  // 0.1: replicated forward, cluster syncs
+        if (cost < best_cost * 0.999) { best_cost = cost; best_csz = csz; best_slots = slots; }
+    }
+    if (best_cost >= 1e300) return fail(ctx, CGNN_ERR_CUDA, "graph kernel cannot be launched (cluster size %d, %zu B smem)", hp->graph_cluster, smem);
+    const int n_clusters = std::min(n_inst, best_slots);
+    ctx->last_cluster = best_csz;
 
     CU(cudaEventRecord(ctx->ev0, ctx->stream));
-    cudaError_t le = launch_graph(DP, HP, hp->exp_policy, a, grid, smem, ctx->stream);
+    cudaError_t le = launch_graph(DP, HP, hp->exp_policy, a, n_clusters, best_csz, smem, ctx->stream, nullptr);
     if (le != cudaSuccess) return fail(ctx, CGNN_ERR_CUDA, "graph kernel launch: %s", cudaGetErrorString(le));
     CU(cudaEventRecord(ctx->ev1, ctx->stream));
     ctx->last_launches = 2;

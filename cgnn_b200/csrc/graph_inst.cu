@@ -1,5 +1,6 @@
 // One translation unit per padded column count (compiled with -DCGNN_DP=8|16|20|24|32): instantiates the
 // graph instance kernel for the four exp policies and exports a launcher + occupancy query.
+#include <algorithm>
 #include "graph.cuh"
 
 #if !defined(CGNN_DP) || !defined(CGNN_HP)
@@ -10,20 +11,32 @@
 
 using namespace cgnn;
 
+// n_clusters < 0: only report, in *max_clusters, how many clusters of `csz` CTAs can be resident at once.
 template <int POL>
-static cudaError_t launch(const GraphArgs& a, int grid, size_t smem, cudaStream_t st) {
+static cudaError_t launch(const GraphArgs& a, int n_clusters, int csz, size_t smem, cudaStream_t st, int* max_clusters) {
     cudaError_t e = cudaFuncSetAttribute(graph_kernel<CGNN_DP, CGNN_HP, POL>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem));
     if (e != cudaSuccess) return e;
-    graph_kernel<CGNN_DP, CGNN_HP, POL><<<grid, GR_NT, smem, st>>>(a);
-    return cudaGetLastError();
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(unsigned(std::max(n_clusters, 1) * csz));
+    cfg.blockDim = dim3(GR_NT);
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = st;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeClusterDimension;
+    at[0].val.clusterDim.x = unsigned(csz); at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+    cfg.attrs = at;
+    cfg.numAttrs = 1;
+    if (n_clusters < 0) return cudaOccupancyMaxActiveClusters(max_clusters, graph_kernel<CGNN_DP, CGNN_HP, POL>, &cfg);
+    return cudaLaunchKernelEx(&cfg, graph_kernel<CGNN_DP, CGNN_HP, POL>, a);
 }
 
-cudaError_t CAT(CAT(cgnn_launch_graph_dp, CGNN_DP), CAT(_hp, CGNN_HP))(int pol, const GraphArgs& a, int grid, size_t smem, cudaStream_t st) {
+cudaError_t CAT(CAT(cgnn_launch_graph_dp, CGNN_DP), CAT(_hp, CGNN_HP))(int pol, const GraphArgs& a, int n_clusters, int csz, size_t smem, cudaStream_t st,
+                                                                   int* max_clusters) {
     switch (pol) {
-        case 0: return launch<0>(a, grid, smem, st);
-        case 1: return launch<1>(a, grid, smem, st);
-        case 2: return launch<2>(a, grid, smem, st);
-        case 3: return launch<3>(a, grid, smem, st);
+        case 0: return launch<0>(a, n_clusters, csz, smem, st, max_clusters);
+        case 1: return launch<1>(a, n_clusters, csz, smem, st, max_clusters);
+        case 2: return launch<2>(a, n_clusters, csz, smem, st, max_clusters);
+        case 3: return launch<3>(a, n_clusters, csz, smem, st, max_clusters);
     }
     return cudaErrorInvalidValue;
 }

@@ -46,6 +46,7 @@ def make_hparams(**kw):
     fast = kw.get("use_Fast_MMD", SETTINGS.use_Fast_MMD)            # GNN.py:47-48, CGNN.py:50-51
     hp.fast_mmd_vectors = int(kw.get("nb_vectors_approx_MMD", SETTINGS.nb_vectors_approx_MMD)) if fast else 0
     hp.seed = int(kw.get("seed", SETTINGS.seed)) & 0xFFFFFFFFFFFFFFFF
+    hp.graph_cluster = int(kw.get("graph_cluster", 0))
     return hp
 
 
@@ -80,6 +81,10 @@ class Engine:
     @property
     def last_launch_count(self):
         return int(self._lib.cgnn_b200_last_launch_count(self._h))
+
+    @property
+    def last_graph_cluster(self):
+        return int(self._lib.cgnn_b200_last_graph_cluster(self._h))
 
     def device_info(self):
         a, b = C.c_int(), C.c_int()

@@ -64,6 +64,9 @@ typedef struct cgnn_hparams {
                                  of Loss.py:35-56 with k = SETTINGS.nb_vectors_approx_MMD vectors per bandwidth
                                  (pairwise path; k <= CGNN_MAX_FAST_VECTORS) */
     unsigned long long seed;  /* engine Philox seed.  The reference is unseeded (no hit for "seed" in its tree). */
+    int   graph_cluster;      /* graph path: CTAs (SMs) per instance, 1..4; 0 = chosen per batch (a thread-block cluster
+                                 when the batch has too few instances to fill the GPU otherwise) */
+    int   reserved1;
 } cgnn_hparams;
 
 /* ---- life cycle ------------------------------------------------------------------------- */
@@ -239,6 +242,9 @@ int  cgnn_b200_probe_peak(cgnn_ctx* ctx, int kind, int reps, double* out_per_sec
 
 /* Number of SMs of the context's device and persistent CTAs per SM the engine launches. */
 int  cgnn_b200_device_info(const cgnn_ctx* ctx, int* n_sm, int* ctas_per_sm_pairwise);
+
+/* CTAs per instance (cluster size) the last cgnn_b200_run_graph call on this context used. */
+int  cgnn_b200_last_graph_cluster(const cgnn_ctx* ctx);
 
 #ifdef __cplusplus
 }

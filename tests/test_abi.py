@@ -28,7 +28,7 @@ def test_library_builds_and_exports_every_declared_symbol():
 
 def test_hparams_struct_layout_matches_header():
     from cgnn_b200 import _lib
-    assert ctypes.sizeof(_lib.Hparams) == 40 and _lib.Hparams.seed.offset == 32
+    assert ctypes.sizeof(_lib.Hparams) == 48 and _lib.Hparams.seed.offset == 32 and _lib.Hparams.graph_cluster.offset == 40
     assert ctypes.sizeof(_lib.GraphBatchStruct) == 16 + 5 * 8
 
 

@@ -189,3 +189,27 @@ def test_generate_matches_oracle_and_fits(engine):
     d = data.values.astype(np.float64)
     d = (d - d.mean(0)) / d.std(0)
     assert mmd.mmd_loss_blocks(d, sample.values) < 0.3 * mmd.mmd_loss_blocks(d, raw.values)
+
+
+def test_cluster_sizes_agree(engine):
+    """One instance on a cluster of 2-4 CTAs (distributed shared memory gradient sum) gives the scores of the
+    single-CTA run: the gradient accumulators are fixed point, so the parameter trajectories are identical."""
+    from cgnn_b200.plan import build_plan
+    n_var = 9
+    g = random_dag(n_var, 2, 8)
+    plan = build_plan(g)
+    data = make_data(700, n_var, 4)          # 22 row blocks: uneven split over 3 and 4 CTAs
+    kw = dict(n_runs=3, h_layer_dim=14, train_epochs=12, test_epochs=4, seed=9, want_params=True, want_trace=True, trace_every=3)
+    base = engine.run_graph(data, [plan, plan], graph_cluster=1, **kw)
+    assert engine.last_graph_cluster == 1
+    for c in (2, 3, 4):
+        r = engine.run_graph(data, [plan, plan], graph_cluster=c, **kw)
+        assert engine.last_graph_cluster == c
+        assert np.array_equal(r["params"], base["params"]), "cluster size %d changed the trained parameters" % c
+        np.testing.assert_allclose(r["scores"], base["scores"], rtol=1e-6)
+        np.testing.assert_allclose(r["trace"], base["trace"], rtol=1e-6, equal_nan=True)
+    # automatic choice: few long instances -> a cluster; many instances -> one CTA each
+    engine.run_graph(make_data(1500, n_var, 1), [plan], n_runs=4, h_layer_dim=10, train_epochs=2, test_epochs=1)
+    assert engine.last_graph_cluster >= 2
+    engine.run_graph(make_data(512, n_var, 2), [plan] * 10, n_runs=32, h_layer_dim=10, train_epochs=1, test_epochs=1)
+    assert engine.last_graph_cluster == 1
