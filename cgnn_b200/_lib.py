@@ -42,7 +42,7 @@ SYMBOLS = {
     "cgnn_b200_run_graph": (C.c_int, [_V, C.POINTER(Hparams), _V, C.c_int, C.POINTER(GraphBatchStruct), C.c_int, _V, C.c_int,
                                       C.c_ulonglong, _V, _V, _V, C.c_int, _V, _V, _V]),
     "cgnn_b200_graph_step_debug": (C.c_int, [_V, C.POINTER(Hparams), _V, C.c_int, C.POINTER(GraphBatchStruct), C.c_int, _V, _V,
-                                             C.c_int, _V, _V, _V, _V, _V]),
+                                             C.c_int, _V, _V, _V, _V, _V, _V]),
     "cgnn_b200_probe_peak": (C.c_int, [_V, C.c_int, C.c_int, C.POINTER(C.c_double)]),
     "cgnn_b200_run_pairwise_noalloc": (C.c_int, [C.c_int, _V, C.POINTER(Hparams), _V, C.c_int, C.c_int, C.c_int,
                                                  C.c_ulonglong, _V, C.c_char_p, C.c_int]),

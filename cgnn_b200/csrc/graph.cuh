@@ -82,14 +82,18 @@ struct GraphArgs {
     float* params_out;         // NULL or [n_inst][ld_params]
     int* counter;
     float *dbg_loss, *dbg_pred, *dbg_dldp, *dbg_grad, *dbg_params;
+    // random-feature ("Fourier") MMD, Loss.py:35-56: fast_k = nb_vectors_approx_MMD, 0 = Gaussian-kernel MMD
+    int fast_k;
+    const float* wz_ext;       // NULL or [n_inst][epochs][n_var+1][7*fast_k]: the matrix of Loss.py:35-37 per step
 };
 
 struct GrSmem {
     float* Pm; float* nbuf; float* theta; float* am; float* av; long long* g64; double* red; GraphDesc* desc;
     int nn_pad;
+    float* Wc; float* bc; float* coef; long long* et; long long* ep;     // random-feature mode: one bandwidth group
 };
 
-__host__ __device__ inline size_t gr_smem_bytes(int NP, int DP, int n_noise, int p_max) {
+__host__ __device__ inline size_t gr_smem_bytes(int NP, int DP, int n_noise, int p_max, int fast_k = 0) {
     const int nn_pad = (n_noise + 3) & ~3;
     const int pp = (p_max + 3) & ~3;
     size_t b = 0;
@@ -99,6 +103,8 @@ __host__ __device__ inline size_t gr_smem_bytes(int NP, int DP, int n_noise, int
     b += size_t(GR_NW) * nn_pad * 32 * 4;         // nbuf
     b += size_t(pp) * 4 * 3;                      // theta, m, v
     b += (sizeof(GraphDesc) + 15) & ~size_t(15);
+    const int kp = (fast_k + 3) & ~3;
+    b += size_t(kp) * (8 + 8 + 4 * DP + 4 + 4);  // et, ep, Wc, bc, coef
     return (b + 15) & ~size_t(15);
 }
 
@@ -303,6 +309,108 @@ __device__ __forceinline__ void gr_backward_block(const GrSmem& s, const float* 
     }
 }
 
+// ---- random-feature ("Fourier") MMD for the graph path (Loss.py:35-56) ------------------------------
+// The 7k features are processed one bandwidth group (k features) at a time: draw the group's frequencies
+// and phases, column sums of cos over the rows (observed and generated), coefficients, per-row gradient.
+// A warp owns exactly one row block in this mode (the host picks the cluster size accordingly), so the
+// row's gradient stays in registers across the seven groups.
+constexpr uint32_t GR_STREAM_FEAT = 900u;
+
+__device__ __forceinline__ float gr_turn_reduce(float z) {
+    const float t = z * 0.15915494309189535f;
+    return (t - rintf(t)) * 6.283185307179586f;
+}
+
+template <int DP>
+__device__ __forceinline__ void gr_fourier_features(const GrSmem& s, const GraphArgs& a, int grp, int step, unsigned int uid,
+                                                    uint2 key, const float* wz_step, int tid) {
+    const int k = a.fast_k, F = 7 * k, nv = s.desc->n_var;
+    const float gam[7] = {G0, G1, G2, G3, G4, G5, G6};
+    const float g2 = 2.0f * gam[grp];
+    for (int w = tid; w < k * (DP / 4 + 1); w += GR_NT) {
+        const int f = w / (DP / 4 + 1), q = w - f * (DP / 4 + 1);
+        const int fid = grp * k + f;
+        if (q == DP / 4) {          // phase, and clear the column sums
+            float b;
+            if (wz_step) b = wz_step[size_t(nv) * F + fid];
+            else b = 6.283185307179586f * u01(philox4x32_10(make_uint4(fid, step, GR_STREAM_FEAT, uid), key).x);
+            s.bc[f] = b; s.et[f] = 0; s.ep[f] = 0;
+        } else {
+            float v[4];
+            if (wz_step) {
+#pragma unroll
+                for (int e = 0; e < 4; ++e) v[e] = (4 * q + e < nv) ? wz_step[size_t(4 * q + e) * F + fid] : 0.f;
+            } else {
+                const float4 n = normal4(philox4x32_10(make_uint4(fid, step, GR_STREAM_FEAT + 1 + q, uid), key));
+                v[0] = g2 * n.x; v[1] = g2 * n.y; v[2] = g2 * n.z; v[3] = g2 * n.w;
+#pragma unroll
+                for (int e = 0; e < 4; ++e) if (4 * q + e >= nv) v[e] = 0.f;
+            }
+            *reinterpret_cast<float4*>(s.Wc + f * DP + 4 * q) = make_float4(v[0], v[1], v[2], v[3]);
+        }
+    }
+}
+
+// z = b + w . row  for a row given as DP/2 pairs
+template <int DP>
+__device__ __forceinline__ float gr_feature_dot(const float2 (&w)[DP / 2], const float (&r)[DP], float b) {
+    float2 za = make_float2(b, 0.f), zb = make_float2(0.f, 0.f);
+#pragma unroll
+    for (int q = 0; q < DP / 2; ++q) {
+        if (q & 1) zb = ffma2(w[q], make_float2(r[2 * q], r[2 * q + 1]), zb);
+        else       za = ffma2(w[q], make_float2(r[2 * q], r[2 * q + 1]), za);
+    }
+    const float2 z = fadd2(za, zb);
+    return z.x + z.y;
+}
+
+// column sums over the rows this CTA owns: work item = (feature, owned row block)
+template <int DP>
+__device__ __forceinline__ void gr_fourier_colsums(const GrSmem& s, const GraphArgs& a, const float* __restrict__ T, int N, int NB,
+                                                   int crank, int csz, int tid) {
+    const int k = a.fast_k;
+    for (int w = tid; w < k * GR_NW; w += GR_NT) {
+        const int slot = w / k, f = w - slot * k;
+        const int rb = crank + csz * slot;
+        if (rb >= NB) continue;
+        float2 wf[DP / 2];
+#pragma unroll
+        for (int q = 0; q < DP / 4; ++q) {
+            const float4 v = *reinterpret_cast<const float4*>(s.Wc + f * DP + 4 * q);
+            wf[2 * q] = make_float2(v.x, v.y); wf[2 * q + 1] = make_float2(v.z, v.w);
+        }
+        const float b = s.bc[f];
+        float st = 0.f, sp = 0.f;
+        const int i1 = min(32 * rb + 32, N);
+        for (int i = 32 * rb; i < i1; ++i) {
+            float r[DP];
+            gr_load_col_gmem<DP>(T, i, r);
+            st += __cosf(gr_turn_reduce(gr_feature_dot<DP>(wf, r, b)));
+            gr_load_col_smem<DP>(s.Pm, i, r);
+            sp += __cosf(gr_turn_reduce(gr_feature_dot<DP>(wf, r, b)));
+        }
+        fx_add(&s.et[f], double(st));
+        fx_add(&s.ep[f], double(sp));
+    }
+}
+
+// per-row gradient of the current feature group, accumulated into acc (lane = row)
+template <int DP>
+__device__ __forceinline__ void gr_fourier_rowgrad(const GrSmem& s, int k, const float (&p)[DP], float2 (&acc)[DP / 2]) {
+    for (int f = 0; f < k; ++f) {
+        float2 wf[DP / 2];
+#pragma unroll
+        for (int q = 0; q < DP / 4; ++q) {
+            const float4 v = *reinterpret_cast<const float4*>(s.Wc + f * DP + 4 * q);
+            wf[2 * q] = make_float2(v.x, v.y); wf[2 * q + 1] = make_float2(v.z, v.w);
+        }
+        const float cs = s.coef[f] * __sinf(gr_turn_reduce(gr_feature_dot<DP>(wf, p, s.bc[f])));
+        const float2 c2 = splat2(cs);
+#pragma unroll
+        for (int q = 0; q < DP / 2; ++q) acc[q] = ffma2(c2, wf[q], acc[q]);
+    }
+}
+
 __device__ __forceinline__ double gr_block_sum(double v, double* red, int warp, int lane) {
     v = warp_sum(v);
     if (lane == 0) red[warp] = v;
@@ -352,7 +460,13 @@ __global__ void __launch_bounds__(GR_NT, 1) graph_kernel(const GraphArgs a) {
         s.theta = reinterpret_cast<float*>(p);     p += size_t(pp) * 4;
         s.am = reinterpret_cast<float*>(p);        p += size_t(pp) * 4;
         s.av = reinterpret_cast<float*>(p);        p += size_t(pp) * 4;
-        s.desc = reinterpret_cast<GraphDesc*>(p);
+        s.desc = reinterpret_cast<GraphDesc*>(p);  p += (sizeof(GraphDesc) + 15) & ~size_t(15);
+        const int kp = (a.fast_k + 3) & ~3;
+        s.et = reinterpret_cast<long long*>(p);    p += size_t(kp) * 8;
+        s.ep = reinterpret_cast<long long*>(p);    p += size_t(kp) * 8;
+        s.Wc = reinterpret_cast<float*>(p);        p += size_t(kp) * DP * 4;
+        s.bc = reinterpret_cast<float*>(p);        p += size_t(kp) * 4;
+        s.coef = reinterpret_cast<float*>(p);
     }
     float* nb = s.nbuf + size_t(warp) * s.nn_pad * 32;
     const int epochs = a.train_epochs + a.test_epochs;
@@ -404,7 +518,9 @@ __global__ void __launch_bounds__(GR_NT, 1) graph_kernel(const GraphArgs a) {
         }
         if (tid == 0) { s.red[GR_NW + 1] = 1.0; s.red[GR_NW + 2] = 1.0; }
         // ---- TT (constant per instance) -------------------------------------------------------
-        {
+        const bool fast = a.fast_k > 0;
+        const float* wz = (fast && a.wz_ext) ? a.wz_ext + size_t(out) * epochs * (s.desc->n_var + 1) * 7 * a.fast_k : nullptr;
+        if (!fast) {
             double part = 0.0;
             for (int rb = rb0; rb < NB; rb += rbs) {
                 const int i = 32 * rb + lane;
@@ -443,53 +559,108 @@ __global__ void __launch_bounds__(GR_NT, 1) graph_kernel(const GraphArgs a) {
                     const int r = q / s.desc->n_var, c = q - r * s.desc->n_var;
                     a.dbg_pred[(size_t(it) * N + r) * s.desc->n_var + c] = s.Pm[r * DP + c];
                 }
-            // ---- loss (evaluation steps; traced training steps) ---------------------------------
-            const bool want_loss = !train || a.dbg_loss || (a.trace && a.trace_every > 0 && it % a.trace_every == 0);
-            if (want_loss) {
-                double part = 0.0;
-                for (int rb = rb0; rb < NB; rb += rbs) {
-                    const int i = 32 * rb + lane;
-                    float pf[DP];
-                    float2 p[DP / 2];
-                    gr_load_col_smem<DP>(s.Pm, i, pf);
+            if (fast) {
+                // ---- random-feature loss: seven bandwidth groups, the row's gradient stays in registers ----------
+                const int i = 32 * rb0 + lane;
+                const bool has = rb0 < NB;                   // this warp's only row block (host: NB <= csz * GR_NW)
+                float pf[DP];
+                float2 acc[DP / 2];
 #pragma unroll
-                    for (int q = 0; q < DP / 2; ++q) p[q] = make_float2(pf[2 * q], pf[2 * q + 1]);
-                    const double v = gr_mmd_eval_row<DP, POL, false>(s.Pm, N, p) - 2.0 * gr_mmd_eval_row<DP, POL, true>(T, N, p);
-                    if (i < N) part += v;
+                for (int q = 0; q < DP / 2; ++q) acc[q] = make_float2(0.f, 0.f);
+                if (has) gr_load_col_smem<DP>(s.Pm, i, pf);
+                else {
+#pragma unroll
+                    for (int c = 0; c < DP; ++c) pf[c] = 0.f;
                 }
-                const double sum = gr_cluster_sum(part, s.red, warp, lane, cl, csz, crank);
+                const float* wz_step = wz ? wz + size_t(it) * (s.desc->n_var + 1) * 7 * a.fast_k : nullptr;
+                const double norm = sqrt(2.0 / double(a.fast_k)) / double(N);
+                double lpart = 0.0;
+                for (int grp = 0; grp < 7; ++grp) {
+                    __syncthreads();                          // the previous group's features are no longer in use
+                    gr_fourier_features<DP>(s, a, grp, it, uid, key, wz_step, tid);
+                    __syncthreads();
+                    gr_fourier_colsums<DP>(s, a, T, N, NB, crank, csz, tid);
+                    if (csz > 1) cl.sync(); else __syncthreads();
+                    for (int f = tid; f < a.fast_k; f += GR_NT) {
+                        long long te = 0, pe = 0;
+                        for (int r = 0; r < csz; ++r) { te += cl.map_shared_rank(s.et, r)[f]; pe += cl.map_shared_rank(s.ep, r)[f]; }
+                        const double diff = norm * (double(te) - double(pe)) * CGNN_FX_INV;      // e1_f - e2_f
+                        lpart += diff * diff;
+                        s.coef[f] = float(2.0 * diff * norm);
+                    }
+                    if (csz > 1) cl.sync(); else __syncthreads();
+                    if (train && has) gr_fourier_rowgrad<DP>(s, a.fast_k, pf, acc);
+                }
+                const double sum = gr_block_sum(lpart, s.red, warp, lane);       // the same in every CTA of the cluster
                 if (tid == 0) {
-                    const float loss = float((sum + s.red[GR_NW]) * invN2);
+                    const float loss = float(sum);
                     if (!train) score_sum += double(loss);
                     if (a.trace && crank == 0) a.trace[size_t(out) * epochs + it] = loss;
                     if (a.dbg_loss && train) a.dbg_loss[it] = loss;
                 }
-            } else if (a.trace && tid == 0 && crank == 0) {
-                a.trace[size_t(out) * epochs + it] = __int_as_float(0x7fc00000);
-            }
-            if (!train) continue;
-            // ---- MMD gradient + generator backward, row block by row block ------------------------
-            for (int rb = rb0; rb < NB; rb += rbs) {
-                const int i = 32 * rb + lane;
+                if (!train) continue;
                 float gl[DP];
-                {
-                    float pf[DP];
-                    float2 p[DP / 2], tot[DP / 2];
-                    gr_load_col_smem<DP>(s.Pm, i, pf);
 #pragma unroll
-                    for (int q = 0; q < DP / 2; ++q) p[q] = make_float2(pf[2 * q], pf[2 * q + 1]);
-                    gr_mmd_train_row<DP, POL>(s.Pm, T, N, p, tot);
-#pragma unroll
-                    for (int q = 0; q < DP / 2; ++q) {
-                        gl[2 * q] = (i < N) ? tot[q].x * scale : 0.f;
-                        gl[2 * q + 1] = (i < N) ? tot[q].y * scale : 0.f;
-                    }
+                for (int q = 0; q < DP / 2; ++q) {
+                    gl[2 * q] = (has && i < N) ? acc[q].x : 0.f;
+                    gl[2 * q + 1] = (has && i < N) ? acc[q].y : 0.f;
                 }
-                if (a.dbg_dldp && i < N)
+                if (a.dbg_dldp && has && i < N)
                     for (int c = 0; c < s.desc->n_var; ++c) a.dbg_dldp[(size_t(it) * N + i) * s.desc->n_var + c] = gl[c];
-                gr_fill_noise(s, a, nb, i, lane, it, uid, key, noise_step);
-                gr_backward_block<DP, HP>(s, nb, i, lane, gl);
-                __syncwarp();
+                if (has) {
+                    gr_fill_noise(s, a, nb, i, lane, it, uid, key, noise_step);
+                    gr_backward_block<DP, HP>(s, nb, i, lane, gl);
+                    __syncwarp();
+                }
+            } else {
+                // ---- loss (evaluation steps; traced training steps) ---------------------------------
+                const bool want_loss = !train || a.dbg_loss || (a.trace && a.trace_every > 0 && it % a.trace_every == 0);
+                if (want_loss) {
+                    double part = 0.0;
+                    for (int rb = rb0; rb < NB; rb += rbs) {
+                        const int i = 32 * rb + lane;
+                        float pf[DP];
+                        float2 p[DP / 2];
+                        gr_load_col_smem<DP>(s.Pm, i, pf);
+    #pragma unroll
+                        for (int q = 0; q < DP / 2; ++q) p[q] = make_float2(pf[2 * q], pf[2 * q + 1]);
+                        const double v = gr_mmd_eval_row<DP, POL, false>(s.Pm, N, p) - 2.0 * gr_mmd_eval_row<DP, POL, true>(T, N, p);
+                        if (i < N) part += v;
+                    }
+                    const double sum = gr_cluster_sum(part, s.red, warp, lane, cl, csz, crank);
+                    if (tid == 0) {
+                        const float loss = float((sum + s.red[GR_NW]) * invN2);
+                        if (!train) score_sum += double(loss);
+                        if (a.trace && crank == 0) a.trace[size_t(out) * epochs + it] = loss;
+                        if (a.dbg_loss && train) a.dbg_loss[it] = loss;
+                    }
+                } else if (a.trace && tid == 0 && crank == 0) {
+                    a.trace[size_t(out) * epochs + it] = __int_as_float(0x7fc00000);
+                }
+                if (!train) continue;
+                // ---- MMD gradient + generator backward, row block by row block ------------------------
+                for (int rb = rb0; rb < NB; rb += rbs) {
+                    const int i = 32 * rb + lane;
+                    float gl[DP];
+                    {
+                        float pf[DP];
+                        float2 p[DP / 2], tot[DP / 2];
+                        gr_load_col_smem<DP>(s.Pm, i, pf);
+    #pragma unroll
+                        for (int q = 0; q < DP / 2; ++q) p[q] = make_float2(pf[2 * q], pf[2 * q + 1]);
+                        gr_mmd_train_row<DP, POL>(s.Pm, T, N, p, tot);
+    #pragma unroll
+                        for (int q = 0; q < DP / 2; ++q) {
+                            gl[2 * q] = (i < N) ? tot[q].x * scale : 0.f;
+                            gl[2 * q + 1] = (i < N) ? tot[q].y * scale : 0.f;
+                        }
+                    }
+                    if (a.dbg_dldp && i < N)
+                        for (int c = 0; c < s.desc->n_var; ++c) a.dbg_dldp[(size_t(it) * N + i) * s.desc->n_var + c] = gl[c];
+                    gr_fill_noise(s, a, nb, i, lane, it, uid, key, noise_step);
+                    gr_backward_block<DP, HP>(s, nb, i, lane, gl);
+                    __syncwarp();
+                }
             }
             // ---- Adam --------------------------------------------------------------------------
             if (csz > 1) {

@@ -49,15 +49,14 @@ static cudaError_t launch_graph(int dp, int hp, int pol, const GraphArgs& a, int
 static int run_graph_impl(cgnn_ctx* ctx, const cgnn_hparams* hp, const float* data, int n_rows_total,
                           const cgnn_graph_batch* gb, int n_runs, const int* row_subsets, int n_rows,
                           unsigned long long uid_base, const unsigned long long* graph_uids, const float* noise, const float* init_params, int ld_params,
-                          float* scores, float* loss_trace, float* params_out, float* const dbg_host[5], int dbg_steps) {
+                          float* scores, float* loss_trace, float* params_out, float* const dbg_host[5], int dbg_steps,
+                          const float* fourier_wz = nullptr) {
     if (!ctx) return CGNN_ERR_ARG;
     ctx->err.clear();
     int rc = check_hp(ctx, hp);
     if (rc) return rc;
     if (hp->h_layer_dim > CGNN_MAX_H_GRAPH)
         return fail(ctx, CGNN_ERR_LIMIT, "graph path: h_layer_dim=%d exceeds CGNN_MAX_H_GRAPH=%d", hp->h_layer_dim, CGNN_MAX_H_GRAPH);
-    if (hp->fast_mmd_vectors != 0)
-        return fail(ctx, CGNN_ERR_LIMIT, "the random-feature loss (use_Fast_MMD) is implemented for the pairwise path only");
     if (!data || !gb) return fail(ctx, CGNN_ERR_ARG, "data / graph batch is NULL");
     if (!gb->node_col || !gb->n_parents || !gb->n_inputs || !gb->in_ptr || !gb->in_idx)
         return fail(ctx, CGNN_ERR_ARG, "graph batch has a NULL array");
@@ -203,12 +202,18 @@ static int run_graph_impl(cgnn_ctx* ctx, const cgnn_hparams* hp, const float* da
         a.dbg_loss = dbg_dev[0]; a.dbg_pred = dbg_dev[1]; a.dbg_dldp = dbg_dev[2]; a.dbg_grad = dbg_dev[3]; a.dbg_params = dbg_dev[4];
     }
 
+    a.fast_k = hp->fast_mmd_vectors;
+    if (fourier_wz) {
+        if (a.fast_k < 1) return fail(ctx, CGNN_ERR_ARG, "fourier_wz given but hparams.fast_mmd_vectors is 0");
+        if ((rc = stage_in(ctx, ctx->wz, fourier_wz, sizeof(float) * size_t(n_inst) * epochs * (n_var + 1) * 7 * a.fast_k, &dp))) return rc;
+        a.wz_ext = static_cast<const float*>(dp);
+    }
     a.n_inst = n_inst; a.N = n_rows; a.NP = NP; a.n_noise = n_noise; a.p_max = p_pad_max;
     a.h = h; a.train_epochs = hp->train_epochs; a.test_epochs = hp->test_epochs; a.trace_every = hp->trace_every;
     a.lr = hp->learning_rate; a.init_std = hp->init_std; a.ld_params = ld_params;
     a.key = make_uint2((unsigned int)(hp->seed & 0xffffffffu), (unsigned int)(hp->seed >> 32));
 
-    const size_t smem = gr_smem_bytes(NP, DP, n_noise, p_pad_max);
+    const size_t smem = gr_smem_bytes(NP, DP, n_noise, p_pad_max, a.fast_k);
     if (smem > size_t(ctx->prop.sharedMemPerBlockOptin))
         return fail(ctx, CGNN_ERR_LIMIT, "graph instance needs %zu B of shared memory (rows %d x cols %d, %d noise columns, %d parameters); "
                     "device allows %zu", smem, n_rows, DP, n_noise, p_max, size_t(ctx->prop.sharedMemPerBlockOptin));
@@ -216,7 +221,11 @@ static int run_graph_impl(cgnn_ctx* ctx, const cgnn_hparams* hp, const float* da
     const int NB = NP / 32;
     int best_csz = 1, best_slots = std::max(1, ctx->prop.multiProcessorCount);
     double best_cost = 1e300;
-    for (int csz = 1; csz <= 4; ++csz) {
+    const int min_csz = a.fast_k > 0 ? (NB + GR_NW - 1) / GR_NW : 1;   // random-feature mode: one row block per warp
+    if (min_csz > 4 || (dbg_host && min_csz > 1))
+        return fail(ctx, CGNN_ERR_LIMIT, "random-feature loss on the graph path: n_rows=%d needs a cluster of %d CTAs (limit %d)",
+                    n_rows, min_csz, dbg_host ? 1 : 4);
+    for (int csz = min_csz; csz <= 4; ++csz) {
         if (dbg_host && csz > 1) break;                              // the parity probe runs on one CTA
         if (hp->graph_cluster > 0 && csz != hp->graph_cluster) continue;
         int slots = 0;
@@ -262,8 +271,8 @@ int cgnn_b200_run_graph(cgnn_ctx* ctx, const cgnn_hparams* hp, const float* data
 
 int cgnn_b200_graph_step_debug(cgnn_ctx* ctx, const cgnn_hparams* hp, const float* data, int n_rows,
                                const cgnn_graph_batch* graph, int n_steps, const float* noise, const float* init_params,
-                               int n_params, float* out_loss, float* out_pred, float* out_dldp, float* out_grad,
-                               float* out_params) {
+                               int n_params, const float* fourier_wz, float* out_loss, float* out_pred, float* out_dldp,
+                               float* out_grad, float* out_params) {
     if (!ctx) return CGNN_ERR_ARG;
     if (!hp) return fail(ctx, CGNN_ERR_ARG, "hparams is NULL");
     if (!noise || !init_params) return fail(ctx, CGNN_ERR_ARG, "step_debug needs caller-supplied noise and parameters");
@@ -274,7 +283,7 @@ int cgnn_b200_graph_step_debug(cgnn_ctx* ctx, const cgnn_hparams* hp, const floa
     h2.trace_every = 0;
     float* dbg[5] = {out_loss, out_pred, out_dldp, out_grad, out_params};
     return run_graph_impl(ctx, &h2, data, n_rows, graph, 1, nullptr, n_rows, 0ULL, nullptr, noise, init_params, n_params, nullptr,
-                          nullptr, nullptr, dbg, n_steps);
+                          nullptr, nullptr, dbg, n_steps, fourier_wz);
 }
 
 }  // extern "C"

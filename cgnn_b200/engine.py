@@ -212,8 +212,9 @@ class Engine:
         self._check(rc, "cgnn_b200_run_graph")
         return dict(scores=scores, trace=trace, params=pout)
 
-    def graph_step_debug(self, data, plan, noise, init_params, **kw):
-        """Parity probe: consecutive train steps of ONE graph instance."""
+    def graph_step_debug(self, data, plan, noise, init_params, fourier_wz=None, **kw):
+        """Parity probe: consecutive train steps of ONE graph instance.
+        fourier_wz [n_steps, n_var+1, 7k]: with use_Fast_MMD=True, the random matrix of Loss.py:35-37 per step."""
         from .plan import GraphBatch, n_params
         hp = make_hparams(**kw)
         data = np.ascontiguousarray(data, np.float32)
@@ -227,8 +228,11 @@ class Engine:
         out = dict(loss=np.empty(n_steps, np.float32), pred=np.empty((n_steps, n_rows, n_var), np.float32),
                    dldp=np.empty((n_steps, n_rows, n_var), np.float32), grad=np.empty((n_steps, P), np.float32),
                    params=np.empty((n_steps, P), np.float32))
+        if fourier_wz is not None:
+            fourier_wz = np.ascontiguousarray(fourier_wz, np.float32)
+            assert fourier_wz.shape == (n_steps, n_var + 1, 7 * hp.fast_mmd_vectors)
         rc = self._lib.cgnn_b200_graph_step_debug(self._h, C.byref(hp), _ptr(data), n_rows, C.byref(gb.struct), n_steps,
-                                                  _ptr(noise), _ptr(init_params), P, _ptr(out["loss"]), _ptr(out["pred"]),
+                                                  _ptr(noise), _ptr(init_params), P, _ptr(fourier_wz), _ptr(out["loss"]), _ptr(out["pred"]),
                                                   _ptr(out["dldp"]), _ptr(out["grad"]), _ptr(out["params"]))
         self._check(rc, "cgnn_b200_graph_step_debug")
         return out

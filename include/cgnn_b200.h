@@ -62,7 +62,7 @@ typedef struct cgnn_hparams {
                                  train step into loss_trace (GNN.py:98-102 prints every 100th); 0 = never */
     int   fast_mmd_vectors;   /* 0: Gaussian-kernel MMD (SETTINGS.use_Fast_MMD = False).  k > 0: the random-feature loss
                                  of Loss.py:35-56 with k = SETTINGS.nb_vectors_approx_MMD vectors per bandwidth
-                                 (pairwise path; k <= CGNN_MAX_FAST_VECTORS) */
+                                 (k <= CGNN_MAX_FAST_VECTORS; on the graph path n_rows <= 2048) */
     unsigned long long seed;  /* engine Philox seed.  The reference is unseeded (no hit for "seed" in its tree). */
     int   graph_cluster;      /* graph path: CTAs (SMs) per instance, 1..4; 0 = chosen per batch (a thread-block cluster
                                  when the batch has too few instances to fill the GPU otherwise) */
@@ -192,6 +192,7 @@ int  cgnn_b200_run_graph(cgnn_ctx* ctx, const cgnn_hparams* hp,
 int  cgnn_b200_graph_step_debug(cgnn_ctx* ctx, const cgnn_hparams* hp,
                                 const float* data, int n_rows, const cgnn_graph_batch* graph, int n_steps,
                                 const float* noise, const float* init_params, int n_params,
+                                const float* fourier_wz,   /* NULL, or [n_steps][n_var+1][7k] with hp->fast_mmd_vectors = k */
                                 float* out_loss, float* out_pred, float* out_dldp,
                                 float* out_grad, float* out_params);
 

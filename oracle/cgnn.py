@@ -85,13 +85,17 @@ def forward_torch(theta, noise, plan, h):
     return torch.cat(cols, 1)                                      # :86-90
 
 
-def step_debug(theta0, data, noise, plan, h, dtype=torch.float64):
+def step_debug(theta0, data, noise, plan, h, dtype=torch.float64, wz=None, k=None):
     th = torch.as_tensor(np.asarray(theta0), dtype=dtype).clone().requires_grad_(True)
     d = torch.as_tensor(np.asarray(data), dtype=dtype)
     nz = torch.as_tensor(np.asarray(noise), dtype=dtype)
     pred = forward_torch(th, nz, plan, h)
     pred.retain_grad()
-    loss = mmd_loss_literal(d, pred)                               # CGNN.py:95
+    if wz is None:
+        loss = mmd_loss_literal(d, pred)                           # CGNN.py:95
+    else:
+        from .mmd import fourier_mmd_literal
+        loss = fourier_mmd_literal(d, pred, torch.as_tensor(np.asarray(wz), dtype=dtype), k)      # CGNN.py:93
     loss.backward()
     return dict(loss=float(loss.detach()), pred=pred.detach().numpy().copy(),
                 dloss_dpred=pred.grad.numpy().copy(), grad=th.grad.numpy().copy())

@@ -213,3 +213,46 @@ def test_cluster_sizes_agree(engine):
     assert engine.last_graph_cluster >= 2
     engine.run_graph(make_data(512, n_var, 2), [plan] * 10, n_runs=32, h_layer_dim=10, train_epochs=1, test_epochs=1)
     assert engine.last_graph_cluster == 1
+
+
+# ---- random-feature ("Fourier") MMD on the graph path (CGNN.py:92-93, Loss.py:35-56) ----------------------
+FTOL = 2e-4        # fp32 floor of this loss, see tests/test_pairwise_gpu.py
+
+
+@pytest.mark.parametrize("n,n_var,h,k,conf", [(100, 5, 8, 6, False), (500, 22, 20, 100, False), (130, 19, 20, 10, True), (33, 3, 32, 3, False)])
+def test_graph_fourier_step_matches_oracle(engine, n, n_var, h, k, conf):
+    from cgnn_b200.plan import build_plan, n_params
+    from oracle import cgnn as oc
+    from oracle.mmd import rp_literal
+    g = random_dag(n_var, 3, 3 * n_var + n, with_skeleton=conf)
+    plan = build_plan(g, confounders=conf)
+    oplan = oc.build_plan(g, confounders=conf)
+    data = make_data(n, n_var, n)
+    rng = np.random.RandomState(n + n_var)
+    theta0 = (0.05 * rng.standard_normal(n_params(plan, h))).astype(np.float32)
+    steps = 2
+    noise = rng.standard_normal((steps, plan["n_noise"], n)).astype(np.float32)
+    wz = np.stack([rp_literal(k, n_var, rng) for _ in range(steps)]).astype(np.float32)
+    got = engine.graph_step_debug(data, plan, noise, theta0, fourier_wz=wz, h_layer_dim=h, use_Fast_MMD=True, nb_vectors_approx_MMD=k)
+    for s in range(steps):
+        th = theta0 if s == 0 else got["params"][s - 1]
+        r = oc.step_debug(th.astype(np.float64), data.astype(np.float64), noise[s].astype(np.float64), oplan, h,
+                          wz=wz[s].astype(np.float64), k=k)
+        assert abs(got["loss"][s] - r["loss"]) <= FTOL * abs(r["loss"]), (s, got["loss"][s], r["loss"])
+        assert relerr(got["dldp"][s], r["dloss_dpred"]) < FTOL
+        assert relerr(got["grad"][s], r["grad"]) < FTOL
+
+
+def test_graph_fourier_runs_on_clusters(engine):
+    """N = 1500 needs three CTAs per instance in this mode; cluster sizes must agree bit for bit."""
+    from cgnn_b200.plan import build_plan
+    n_var = 6
+    plan = build_plan(random_dag(n_var, 2, 2))
+    kw = dict(n_runs=2, h_layer_dim=10, train_epochs=6, test_epochs=3, seed=4, use_Fast_MMD=True, nb_vectors_approx_MMD=20,
+              want_params=True)
+    small = make_data(480, n_var, 3)
+    a = engine.run_graph(small, [plan], graph_cluster=1, **kw)
+    b = engine.run_graph(small, [plan], graph_cluster=3, **kw)
+    assert np.array_equal(a["params"], b["params"]) and np.allclose(a["scores"], b["scores"], rtol=1e-6)
+    big = engine.run_graph(make_data(1500, n_var, 5), [plan], **kw)
+    assert engine.last_graph_cluster >= 3 and np.all(np.isfinite(big["scores"])) and np.all(big["scores"] > 0)
