@@ -70,7 +70,8 @@ def score_pairs(pairs, idx0=0, **kwargs):
 
     uid0 = int(kwargs.get("uid_base", 0)) + idx0 * nb_runs * 2
     kw.pop("uid_base", None)
-    scores = runtime.run_sharded(len(slots), runs_per_slot * 2, uid0, call, tail_shape=(runs_per_slot, 2))
+    scores = runtime.run_batch(len(slots), runs_per_slot * 2, uid0, call, tail_shape=(runs_per_slot, 2),
+                               costs=[float(n) * float(n) for n in n_rows])
     return scores.reshape(len(mats), nb_runs, 2)
 
 

@@ -11,7 +11,17 @@ Here a whole batch of independent instances is cut into contiguous shards:
 and the score arrays are put back together with ONE all_gather (NCCL on GPUs, gloo in the CPU
 tests).  No other collective exists on this path.  Every instance draws its random numbers from the
 Philox stream of its GLOBAL index (`uid_base`), so the result is bit-identical for any sharding.
+
+Two schedules:
+  * static (default): equal contiguous shards - optimal when all instances cost the same (one launch
+    per GPU, every SM busy until the common end);
+  * work stealing (`SETTINGS.work_stealing`, or automatically for batches whose items differ in cost):
+    the batch is cut into chunks; every worker (rank x local GPU) starts on "its" chunk - the static
+    round-robin part - and then pulls the next unclaimed chunk from a shared counter: an atomic `add` on
+    the job's c10d store across processes, a locked integer across the GPUs of one process.  Results are
+    merged with one all_reduce(SUM) over a zero-initialised buffer (each item is written by one worker).
 """
+import itertools
 import os
 import threading
 from concurrent.futures import ThreadPoolExecutor
@@ -112,3 +122,84 @@ def run_sharded(n_items, items_per_uid, uid_base, call, tail_shape=()):
     if local is None:                                          # more ranks than items
         local = np.zeros((0,) + tuple(tail_shape), np.float32)
     return all_gather_concat(local, counts)
+
+
+_CALL_SEQ = itertools.count()
+
+
+class _ChunkQueue(object):
+    """Next-unclaimed-chunk counter shared by every worker of the job."""
+
+    def __init__(self, n_chunks, n_workers_total, first_worker, n_local):
+        self.n_chunks, self.total = n_chunks, n_workers_total
+        self.first, self.n_local = first_worker, n_local
+        self.key = "cgnn_b200/steal/%d" % next(_CALL_SEQ)         # all ranks call in lockstep -> same key
+        self.lock = threading.Lock()
+        self.local_next = n_workers_total                          # chunks 0..total-1 are the static first picks
+        _, world = dist_info()
+        self.store = None
+        if world > 1:
+            import torch.distributed as dist
+            self.store = dist.distributed_c10d._get_default_store()
+
+    def first_pick(self, local_worker):
+        c = self.first + local_worker
+        return c if c < self.n_chunks else None
+
+    def steal(self):
+        if self.store is not None:
+            c = self.total + self.store.add(self.key, 1) - 1       # atomic across processes
+        else:
+            with self.lock:
+                c = self.local_next
+                self.local_next += 1
+        return c if c < self.n_chunks else None
+
+
+def run_stolen(n_items, items_per_uid, uid_base, call, tail_shape=(), chunk_items=None):
+    """Like run_sharded, with the chunked work-stealing schedule.  `chunk_items`: items per chunk (default:
+    about four chunks per worker)."""
+    rank, world = dist_info()
+    engines = get_engines()
+    n_local = len(engines)
+    total = world * n_local
+    if chunk_items is None:
+        chunk_items = max(1, -(-n_items // (4 * total)))
+    n_chunks = -(-n_items // chunk_items)
+    queue = _ChunkQueue(n_chunks, total, rank * n_local, n_local)
+    out = np.zeros((n_items,) + tuple(tail_shape), np.float32)
+    owned = []
+
+    def worker(k):
+        c = queue.first_pick(k)
+        while c is not None:
+            lo, hi = c * chunk_items, min(n_items, (c + 1) * chunk_items)
+            out[lo:hi] = call(engines[k], lo, hi, uid_base + lo * items_per_uid)
+            owned.append(c)
+            c = queue.steal()
+
+    if n_local == 1:
+        worker(0)
+    else:
+        with ThreadPoolExecutor(n_local) as ex:
+            list(ex.map(worker, range(n_local)))
+    run_stolen.last_owned = sorted(owned)
+    if world == 1:
+        return out
+    import torch
+    import torch.distributed as dist
+    dev = torch.device("cuda", int(os.environ.get("LOCAL_RANK", "0"))) if dist.get_backend() == "nccl" else torch.device("cpu")
+    buf = torch.from_numpy(out).to(dev)
+    dist.all_reduce(buf, op=dist.ReduceOp.SUM)                      # every item was written by exactly one worker
+    return buf.cpu().numpy()
+
+
+def run_batch(n_items, items_per_uid, uid_base, call, tail_shape=(), costs=None):
+    """Static shards for uniform batches, work stealing when asked for or when item costs differ."""
+    steal = bool(getattr(SETTINGS, "work_stealing", False))
+    if costs is not None and len(costs) > 1 and max(costs) > 1.25 * min(costs):
+        steal = True
+    _, world = dist_info()
+    if steal and (world > 1 or len(local_devices()) > 1):
+        return run_stolen(n_items, items_per_uid, uid_base, call, tail_shape)
+    return run_sharded(n_items, items_per_uid, uid_base, call, tail_shape)

@@ -35,7 +35,7 @@ def _worker(rank, world, port, q):
     eng = FakeEngine(rank)
     runtime.get_engines = lambda: [eng]
     rng = np.random.default_rng(0)
-    pairs = [rng.normal(size=(50 + 10 * k, 2)).astype(np.float32) for k in range(5)]
+    pairs = [rng.normal(size=(60, 2)).astype(np.float32) for k in range(5)]          # uniform cost -> static shards
     s = score_pairs(pairs, 0, nb_runs=3)
     g = ths.build_start(my_graph, False)
     from cgnn_b200.CGNN import hill_climbing
@@ -57,7 +57,7 @@ def test_two_gloo_ranks_reproduce_single_process(monkeypatch):
     monkeypatch.setattr(SETTINGS, "verbose", False)
     monkeypatch.setattr(runtime, "get_engines", lambda: [FakeEngine()])
     rng = np.random.default_rng(0)
-    pairs = [rng.normal(size=(50 + 10 * k, 2)).astype(np.float32) for k in range(5)]
+    pairs = [rng.normal(size=(60, 2)).astype(np.float32) for k in range(5)]
     want = score_pairs(pairs, 0, nb_runs=3)
     want_edges = ths._edges(hill_climbing(ths.build_start(my_graph, False), ths._data(False), nb_runs=2))
 
@@ -88,3 +88,62 @@ def test_split_range():
             assert all(cuts[k][1] == cuts[k + 1][0] for k in range(parts - 1))
             sizes = [b - a for a, b in cuts]
             assert max(sizes) - min(sizes) <= 1
+
+
+def _steal_worker(rank, world, port, q):
+    sys.path.insert(0, HERE)
+    sys.path.insert(0, os.path.dirname(HERE))
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world), LOCAL_RANK=str(rank))
+    import time
+    import torch.distributed as dist
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    from fake_engine import FakeEngine
+    from cgnn_b200 import runtime, SETTINGS
+    from cgnn_b200.GNN import score_pairs
+    SETTINGS.verbose = False
+
+    class Slow(FakeEngine):
+        def run_pairwise(self, *a, **k):
+            time.sleep(0.25 if rank == 0 else 0.0)          # rank 0 is the slow GPU: rank 1 must take more chunks
+            return FakeEngine.run_pairwise(self, *a, **k)
+
+    eng = Slow(rank)
+    runtime.get_engines = lambda: [eng]
+    rng = np.random.default_rng(0)
+    pairs = [rng.normal(size=(40 + 30 * (k % 5), 2)).astype(np.float32) for k in range(24)]      # ragged -> stealing schedule
+    s = score_pairs(pairs, 0, nb_runs=2)
+    q.put((rank, s, list(runtime.run_stolen.last_owned)))
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+@pytest.mark.timeout(300)
+def test_work_stealing_over_two_ranks(monkeypatch):
+    """Ragged batch -> chunked schedule: static first pick + atomic counter on the c10d store.  Every chunk is
+    done exactly once, the fast rank does more of them, and the merged scores equal the single-process ones."""
+    import torch.multiprocessing as mp
+    sys.path.insert(0, HERE)
+    from fake_engine import FakeEngine
+    from cgnn_b200 import runtime, SETTINGS
+    from cgnn_b200.GNN import score_pairs
+    monkeypatch.setattr(SETTINGS, "verbose", False)
+    monkeypatch.setattr(runtime, "get_engines", lambda: [FakeEngine()])
+    rng = np.random.default_rng(0)
+    pairs = [rng.normal(size=(40 + 30 * (k % 5), 2)).astype(np.float32) for k in range(24)]
+    want = score_pairs(pairs, 0, nb_runs=2)
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_steal_worker, args=(r, 2, port, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    res = [q.get(timeout=240) for _ in procs]
+    for p in procs:
+        p.join(60)
+        assert p.exitcode == 0
+    owned = {r: o for r, _, o in res}
+    assert sorted(owned[0] + owned[1]) == list(range(8)), owned            # 24 items / (4 chunks x 2 workers) = 3 per chunk
+    assert owned[0][0] == 0 and owned[1][0] == 1                           # static first picks
+    assert len(owned[1]) > len(owned[0])                                   # the fast rank stole more
+    for _, s, _ in res:
+        assert np.array_equal(s, want)
