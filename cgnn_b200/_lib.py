@@ -4,7 +4,7 @@ import ctypes as C
 import os
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "libcgnn_b200.so")
+LIB_PATH = os.environ.get("CGNN_B200_LIB") or os.path.join(HERE, "libcgnn_b200.so")      # env override: tuning experiments
 
 
 class Hparams(C.Structure):

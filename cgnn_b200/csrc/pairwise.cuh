@@ -37,6 +37,11 @@ namespace cgnn {
 #ifndef CGNN_PW_CTAS
 #define CGNN_PW_CTAS 2
 #endif
+#ifndef CGNN_TRIO_UNROLL
+#define CGNN_TRIO_UNROLL 2
+#endif
+#define CGNN_PRAGMA(x) _Pragma(#x)
+#define CGNN_UNROLL(n) CGNN_PRAGMA(unroll n)
 constexpr int PW_NT = CGNN_PW_NT;       // threads per CTA
 constexpr int PW_NW = PW_NT / 32;       // warps per CTA
 constexpr int PW_MIN_CTAS = CGNN_PW_CTAS;
@@ -108,7 +113,7 @@ __device__ __forceinline__ float trio_train(float xi, float yi, float yhi, const
     float2 ra = make_float2(0.f, 0.f);
     float ca = 0.f;
     const int src = (lane + 1) & 31;
-#pragma unroll 2
+    CGNN_UNROLL(CGNN_TRIO_UNROLL)
     for (int s = 0; s < 32; s += 2) {
         const float4 c0 = tile[s], c1 = tile[s + 1];
         const float dx0 = xi - c0.x, dx1 = xi - c1.x;
@@ -149,7 +154,7 @@ __device__ __forceinline__ float duo_train(float xi, float yhi, const float4* __
 template <int POL>
 __device__ __forceinline__ float trio_eval(float xi, float yi, float yhi, const float4* __restrict__ tile) {
     float2 acc = make_float2(0.f, 0.f);
-#pragma unroll 2
+    CGNN_UNROLL(CGNN_TRIO_UNROLL)
     for (int s = 0; s < 32; s += 2) {
         const float4 c0 = tile[s], c1 = tile[s + 1];
         const float dx0 = xi - c0.x, dx1 = xi - c1.x;

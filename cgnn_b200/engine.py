@@ -62,11 +62,15 @@ class Engine:
         self.device = int(device)
 
     def close(self):
-        if getattr(self, "_h", None):
-            self._lib.cgnn_b200_destroy(self._h)
-            self._h = None
+        h, self._h = getattr(self, "_h", None), None
+        if h:
+            try:
+                self._lib.cgnn_b200_destroy(h)
+            except Exception:          # interpreter shutdown: the library may already be unloaded
+                pass
 
-    __del__ = close
+    def __del__(self):
+        self.close()
 
     def _check(self, rc, what):
         if rc != 0:

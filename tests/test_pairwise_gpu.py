@@ -258,3 +258,22 @@ def test_in_kernel_random_streams(engine):
     big = engine.run_pairwise(np.repeat(xy[None], 8, 0), n_runs=8, train_epochs=0, test_epochs=1, h_layer_dim=64,
                               want_params=True)["params"]
     assert abs(big.mean()) < 2e-3 and abs(big.std() - 0.05) < 2e-3
+
+
+def test_nan_inputs_propagate_without_hanging(engine):
+    """Diverged / invalid instances must come back as NaN, never masked and never a hang: the pairwise path of
+    the reference has no finite-filter (GNN.py:196-197), the graph paths filter on the host (CGNN.py:217)."""
+    xy = np.stack([make_pair(100, 1, 0), make_pair(100, 2, 1)])
+    xy[1, 17, 0] = np.nan
+    s = engine.run_pairwise(xy, n_runs=2, h_layer_dim=6, train_epochs=5, test_epochs=2)["scores"]
+    assert np.all(np.isfinite(s[0])) and np.all(np.isnan(s[1]))
+    from cgnn_b200 import GNN, runtime, SETTINGS
+    old = SETTINGS.verbose
+    SETTINGS.verbose = False
+    try:
+        pred = GNN().predict_proba_batch([(xy[0, :, 0], xy[0, :, 1]), (xy[1, :, 0], xy[1, :, 1])], nb_runs=2, h_layer_dim=6,
+                                         train_epochs=5, test_epochs=2)
+    finally:
+        SETTINGS.verbose = old
+        runtime.close_engines()
+    assert np.isfinite(pred[0]) and np.isnan(pred[1])
