@@ -277,3 +277,16 @@ def test_nan_inputs_propagate_without_hanging(engine):
         SETTINGS.verbose = old
         runtime.close_engines()
     assert np.isfinite(pred[0]) and np.isnan(pred[1])
+
+
+def test_many_waves_through_the_instance_queue(engine):
+    """Far more instances than resident CTAs (about 9 waves of the persistent grid): every instance is scored
+    exactly once, whatever CTA picked it up."""
+    n_pairs, runs = 170, 8
+    xy = np.stack([make_pair(96, 500 + p, p % 3) for p in range(n_pairs)])
+    kw = dict(n_runs=runs, h_layer_dim=5, train_epochs=3, test_epochs=2, seed=8)
+    big = engine.run_pairwise(xy, **kw)["scores"]
+    assert big.shape == (n_pairs, runs, 2) and np.all(np.isfinite(big)) and np.all(big > 0)
+    for p in (0, 57, 169):
+        one = engine.run_pairwise(xy[p:p + 1], uid_base=p * runs * 2, **kw)["scores"]
+        assert np.array_equal(big[p:p + 1], one)
