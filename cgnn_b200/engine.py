@@ -28,10 +28,6 @@ def _ptr(a):
     return C.c_void_p(a.data_ptr())          # torch.Tensor
 
 
-def _is_torch(a):
-    return a is not None and not isinstance(a, np.ndarray) and hasattr(a, "data_ptr")
-
-
 def make_hparams(**kw):
     """cgnn_hparams from SETTINGS with the reference's kwargs-override rule
     (GNN.py:45-48,90,112; CGNN.py:48-51,115,137): the same names, per call."""

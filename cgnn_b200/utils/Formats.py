@@ -25,15 +25,3 @@ def CCEPC_PairsFileReader(filename, scale=True):
             a, b = _standardise(a), _standardise(b)
         rows.append((sample_id, a, b))
     return DataFrame(rows, columns=["SampleID", "A", "B"])
-
-
-def pairs_to_batch(df, max_points=None, rng=None):
-    """Stack the pairs of a CEPC DataFrame into the engine's batch layout:
-    (xy float32 [n_pairs, ld_rows, 2], n_rows int32 [n_pairs])."""
-    n = [len(a) for a in df["A"]]
-    ld = max(n)
-    xy = np.zeros((len(n), ld, 2), np.float32)
-    for k, (a, b) in enumerate(zip(df["A"], df["B"])):
-        xy[k, :n[k], 0] = a
-        xy[k, :n[k], 1] = b
-    return xy, np.asarray(n, np.int32)
