@@ -33,7 +33,10 @@ extern "C" {
 #define CGNN_MAX_H_GRAPH       32       /* hidden width limit of the graph path (reference default 20) */
 #define CGNN_MAX_VARS          32       /* variables (columns) per graph */
 #define CGNN_MAX_FAST_VECTORS  256      /* nb_vectors_approx_MMD limit of the random-feature loss (reference default 100) */
-#define CGNN_MAX_ROWS_GRAPH    1536     /* rows per graph instance after subsampling (SETTINGS.max_nb_points = 1500) */
+#define CGNN_MAX_ROWS_GRAPH    1536     /* rows per graph instance after subsampling (SETTINGS.max_nb_points = 1500).
+                                           One graph instance must also fit one SM's shared memory (227 KB):
+                                           rows x vars x 4 B + 2 KB per noise column + 20 B per (padded) parameter;
+                                           e.g. 1536 x 20, h = 20 fits, 1536 x 32 does not (CGNN_ERR_LIMIT with the sizes) */
 
 typedef enum cgnn_status {
     CGNN_OK            =  0,

@@ -256,3 +256,20 @@ def test_graph_fourier_runs_on_clusters(engine):
     assert np.array_equal(a["params"], b["params"]) and np.allclose(a["scores"], b["scores"], rtol=1e-6)
     big = engine.run_graph(make_data(1500, n_var, 5), [plan], **kw)
     assert engine.last_graph_cluster >= 3 and np.all(np.isfinite(big["scores"])) and np.all(big["scores"] > 0)
+
+
+def test_graph_size_limits(engine):
+    """Largest shapes: 1536 rows x 20 variables fits; combinations that exceed one SM's shared memory are
+    refused with a message that says so (no silent truncation, no crash)."""
+    from cgnn_b200 import EngineError
+    from cgnn_b200.plan import build_plan
+    plan20 = build_plan(random_dag(20, 2, 6))
+    r = engine.run_graph(make_data(1536, 20, 1), [plan20], n_runs=2, h_layer_dim=20, train_epochs=2, test_epochs=1)
+    assert np.all(np.isfinite(r["scores"]))
+    plan32 = build_plan(random_dag(32, 3, 7))
+    with pytest.raises(EngineError, match="shared memory"):
+        engine.run_graph(make_data(1536, 32, 1), [plan32], n_runs=1, h_layer_dim=32, train_epochs=1, test_epochs=1)
+    r = engine.run_graph(make_data(512, 32, 2), [plan32], n_runs=1, h_layer_dim=20, train_epochs=2, test_epochs=1)
+    assert np.all(np.isfinite(r["scores"]))
+    with pytest.raises(EngineError):
+        engine.run_graph(make_data(64, 33, 2), [build_plan(random_dag(33, 2, 8))], n_runs=1)

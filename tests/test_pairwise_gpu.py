@@ -290,3 +290,16 @@ def test_many_waves_through_the_instance_queue(engine):
     for p in (0, 57, 169):
         one = engine.run_pairwise(xy[p:p + 1], uid_base=p * runs * 2, **kw)["scores"]
         assert np.array_equal(big[p:p + 1], one)
+
+
+def test_maximum_rows_pairwise(engine):
+    """CGNN_MAX_ROWS_PAIRWISE = 2048 rows: one step against the oracle (the reference never exceeds 1500)."""
+    n, h = 2048, 20
+    rng = np.random.default_rng(12)
+    xy = make_pair(n, 77, kind=2)
+    theta0 = (0.05 * rng.normal(size=4 * h + 1)).astype(np.float32)
+    noise = rng.normal(size=(1, n)).astype(np.float32)
+    got = engine.pairwise_step_debug(xy, noise, theta0, h_layer_dim=h)
+    ref = _oracle_train(xy, noise, theta0, h)
+    assert abs(got["loss"][0] - ref["loss"][0]) <= TOL * abs(ref["loss"][0])
+    assert relerr(got["dldy"][0], ref["dldy"][0]) < TOL and relerr(got["grad"][0], ref["grad"][0]) < TOL
