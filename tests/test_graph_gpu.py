@@ -273,3 +273,29 @@ def test_graph_size_limits(engine):
     assert np.all(np.isfinite(r["scores"]))
     with pytest.raises(EngineError):
         engine.run_graph(make_data(64, 33, 2), [build_plan(random_dag(33, 2, 8))], n_runs=1)
+
+
+@pytest.mark.parametrize("pol", [0, 3])
+def test_graph_trained_state_parity(engine, pol):
+    """After 150 Adam steps the loss has dropped and dLoss/dPred is a small difference of large PT / PP sums:
+    the case that stresses the fp32 accumulation scheme (re-anchored on the kernel's own parameters)."""
+    from cgnn_b200.plan import build_plan, n_params
+    from oracle import cgnn as oc
+    n, n_var, h, steps = 256, 6, 12, 150
+    g = random_dag(n_var, 2, 21)
+    plan = build_plan(g)
+    oplan = oc.build_plan(g)
+    rng = np.random.default_rng(6)
+    # data that the graph can actually fit: sampled from a random generator of the same structure
+    th_gen = (0.8 * rng.normal(size=n_params(plan, h))).astype(np.float64)
+    data = oc.generate(th_gen, rng.normal(size=(plan["n_noise"], n)), oplan, h)
+    data = ((data - data.mean(0)) / data.std(0)).astype(np.float32)
+    theta0 = (0.05 * rng.normal(size=n_params(plan, h))).astype(np.float32)
+    noise = rng.normal(size=(steps, plan["n_noise"], n)).astype(np.float32)
+    got = engine.graph_step_debug(data, plan, noise, theta0, h_layer_dim=h, exp_policy=pol)
+    assert got["loss"][-1] < 0.5 * got["loss"][0]
+    th = got["params"][steps - 2].astype(np.float64)
+    r = oc.step_debug(th, data.astype(np.float64), noise[steps - 1].astype(np.float64), oplan, h)
+    assert abs(got["loss"][-1] - r["loss"]) <= TOL * abs(r["loss"]), (got["loss"][-1], r["loss"])
+    assert relerr(got["dldp"][-1], r["dloss_dpred"]) < TOL
+    assert relerr(got["grad"][-1], r["grad"]) < TOL
