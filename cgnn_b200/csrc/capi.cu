@@ -226,9 +226,8 @@ static int run_pairwise_impl(cgnn_ctx* ctx, const cgnn_hparams* hp, const float*
     a.n_inst = n_inst; a.ld_rows = ld_rows; a.np_max = 32 * ((max_n + 31) / 32);
     a.h = h; a.train_epochs = hp->train_epochs; a.test_epochs = hp->test_epochs; a.trace_every = hp->trace_every;
     a.lr = hp->learning_rate; a.init_std = hp->init_std;
-    a.key = make_uint2((unsigned int)(hp->seed & 0xffffffffu),
-                       (unsigned int)(hp->seed >> 32) ^ (unsigned int)(uid_base >> 32));
-    a.uid_base = (unsigned int)(uid_base & 0xffffffffu);
+    a.key = make_uint2((unsigned int)(hp->seed & 0xffffffffu), (unsigned int)(hp->seed >> 32));
+    a.uid_base = uid_base;
 
     const size_t smem = pw_smem_bytes(a.np_max, h, a.fast_k);
     if (smem > size_t(ctx->prop.sharedMemPerBlockOptin))
@@ -411,8 +410,8 @@ extern "C" int cgnn_b200_run_pairwise_noalloc(int device, void* stream, const cg
     a.n_inst = n_inst; a.ld_rows = n_rows; a.np_max = 32 * ((n_rows + 31) / 32);
     a.h = hp->h_layer_dim; a.train_epochs = hp->train_epochs; a.test_epochs = hp->test_epochs; a.trace_every = 0;
     a.lr = hp->learning_rate; a.init_std = hp->init_std;
-    a.key = make_uint2((unsigned int)(hp->seed & 0xffffffffu), (unsigned int)(hp->seed >> 32) ^ (unsigned int)(uid_base >> 32));
-    a.uid_base = (unsigned int)(uid_base & 0xffffffffu);
+    a.key = make_uint2((unsigned int)(hp->seed & 0xffffffffu), (unsigned int)(hp->seed >> 32));
+    a.uid_base = uid_base;
     a.scores = d_scores;
     a.fast_k = hp->fast_mmd_vectors;
 

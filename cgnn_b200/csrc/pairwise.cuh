@@ -55,8 +55,8 @@ struct PairwiseArgs {
     int n_inst, ld_rows, np_max;
     int h, train_epochs, test_epochs, trace_every;
     float lr, init_std;
-    uint2 key;
-    unsigned int uid_base;
+    uint2 key;                  // Philox key = seed; the high half of the 64-bit instance uid is xor-ed into key.y
+    unsigned long long uid_base;
     const float* noise;       // NULL or [n_inst][epochs][ld_rows]   (indexed by out_index)
     const float* init_params; // NULL or [n_inst][4h+1]
     float* scores;            // [n_inst] by out_index
@@ -268,13 +268,13 @@ __device__ __forceinline__ float pw_turn_reduce(float z) {       // z radians ->
 
 // draw (or fetch) the features of this step and clear the column sums
 __device__ __forceinline__ void pw_fourier_features(const PwSmem& s, const PairwiseArgs& a, int F, int step,
-                                                    unsigned int uid, const float* wz_step, int tid) {
+                                                    unsigned int uid, uint2 key, const float* wz_step, int tid) {
     const float gam[7] = {G0, G1, G2, G3, G4, G5, G6};
     for (int f = tid; f < F; f += PW_NT) {
         float wx, wy, b;
         if (wz_step) { wx = wz_step[f]; wy = wz_step[F + f]; b = wz_step[2 * F + f]; }
         else {
-            const uint4 r = philox4x32_10(make_uint4(f, step, STREAM_FEAT, uid), a.key);
+            const uint4 r = philox4x32_10(make_uint4(f, step, STREAM_FEAT, uid), key);
             const float4 n = normal4(r);
             const float g2 = 2.0f * gam[f / a.fast_k];
             wx = g2 * n.x; wy = g2 * n.y;
@@ -349,7 +349,7 @@ __device__ __forceinline__ double block_sum(double v, double* red, int warp, int
 
 // Generator forward for 4-row quads (GNN.py:64-67), noise from Philox or the caller.
 __device__ __forceinline__ void pw_forward(const PwSmem& s, const PairwiseArgs& a, int N, int NP, int h, int step,
-                                           unsigned int uid, const float* noise_row, int tid) {
+                                           unsigned int uid, uint2 key, const float* noise_row, int tid) {
     for (int q = tid; 4 * q < NP; q += PW_NT) {
         const int r0 = 4 * q;
         s.g64[r0] = 0; s.g64[r0 + 1] = 0; s.g64[r0 + 2] = 0; s.g64[r0 + 3] = 0;
@@ -359,7 +359,7 @@ __device__ __forceinline__ void pw_forward(const PwSmem& s, const PairwiseArgs& 
 #pragma unroll
             for (int r = 0; r < 4; ++r) e[r] = (r0 + r < N) ? noise_row[r0 + r] : 0.f;
         } else {
-            const float4 n = normal4(philox4x32_10(make_uint4(q, step, STREAM_NOISE, uid), a.key));
+            const float4 n = normal4(philox4x32_10(make_uint4(q, step, STREAM_NOISE, uid), key));
             e[0] = n.x; e[1] = n.y; e[2] = n.z; e[3] = n.w;
         }
         float x[4], y[4];
@@ -478,7 +478,9 @@ __global__ void __launch_bounds__(PW_NT, PW_MIN_CTAS) pairwise_kernel(const Pair
         if (it_idx >= a.n_inst) break;
         const int4 inst = a.inst[it_idx];
         const int pair = inst.x, dir = inst.z, out = inst.w;
-        const unsigned int uid = a.uid_base + (unsigned int)out;
+        const unsigned long long uid64 = a.uid_base + (unsigned long long)out;
+        const unsigned int uid = (unsigned int)(uid64 & 0xffffffffull);
+        const uint2 key = make_uint2(a.key.x, a.key.y ^ (unsigned int)(uid64 >> 32));
         const int N = a.n_rows[pair];
         const int NB = (N + 31) >> 5, NP = NB * 32;
         const float* src = a.xy + size_t(pair) * a.ld_rows * 2;
@@ -505,7 +507,7 @@ __global__ void __launch_bounds__(PW_NT, PW_MIN_CTAS) pairwise_kernel(const Pair
             if (p < P) {
                 if (a.init_params) th = a.init_params[size_t(out) * P + p];
                 else {
-                    const float4 n = normal4(philox4x32_10(make_uint4(p >> 2, 0u, STREAM_INIT, uid), a.key));
+                    const float4 n = normal4(philox4x32_10(make_uint4(p >> 2, 0u, STREAM_INIT, uid), key));
                     const int e = p & 3;
                     th = a.init_std * (e == 0 ? n.x : e == 1 ? n.y : e == 2 ? n.z : n.w);
                 }
@@ -534,12 +536,12 @@ __global__ void __launch_bounds__(PW_NT, PW_MIN_CTAS) pairwise_kernel(const Pair
                 s.red[PW_NW + 1] = b1p; s.red[PW_NW + 2] = b2p;
                 s.red[PW_NW + 3] = double(a.lr) * sqrt(1.0 - b2p) / (1.0 - b1p);
             }
-            pw_forward(s, a, N, NP, h, it, uid, noise ? noise + size_t(it) * a.ld_rows : nullptr, tid);
+            pw_forward(s, a, N, NP, h, it, uid, key, noise ? noise + size_t(it) * a.ld_rows : nullptr, tid);
             __syncthreads();
             const bool traced = a.dbg_loss || (a.trace && a.trace_every > 0 && it % a.trace_every == 0);
             if (a.dbg_yhat) for (int i = tid; i < N; i += PW_NT) a.dbg_yhat[size_t(it) * N + i] = s.yh[i];
             if (fast) {   // random-feature loss: the loss value is a by-product of the gradient
-                pw_fourier_features(s, a, F, it, uid, wz ? wz + size_t(it) * 3 * F : nullptr, tid);
+                pw_fourier_features(s, a, F, it, uid, key, wz ? wz + size_t(it) * 3 * F : nullptr, tid);
                 __syncthreads();
                 pw_fourier_colsums(s, N, NB, F, tid);
                 __syncthreads();
@@ -591,12 +593,12 @@ __global__ void __launch_bounds__(PW_NT, PW_MIN_CTAS) pairwise_kernel(const Pair
         double score_sum = 0.0;
         for (int it = 0; it < a.test_epochs; ++it) {
             __syncthreads();
-            pw_forward(s, a, N, NP, h, a.train_epochs + it, uid,
+            pw_forward(s, a, N, NP, h, a.train_epochs + it, uid, key,
                        noise ? noise + size_t(a.train_epochs + it) * a.ld_rows : nullptr, tid);
             __syncthreads();
             double sum;
             if (fast) {
-                pw_fourier_features(s, a, F, a.train_epochs + it, uid, wz ? wz + size_t(a.train_epochs + it) * 3 * F : nullptr, tid);
+                pw_fourier_features(s, a, F, a.train_epochs + it, uid, key, wz ? wz + size_t(a.train_epochs + it) * 3 * F : nullptr, tid);
                 __syncthreads();
                 pw_fourier_colsums(s, N, NB, F, tid);
                 __syncthreads();

@@ -119,6 +119,12 @@ def test_determinism_and_batch_cut_invariance(engine):
     assert np.array_equal(a, np.concatenate([c0, c1]))
     d = engine.run_pairwise(xy, **dict(kw, seed=99))["scores"]
     assert not np.array_equal(a, d)
+    # the instance id is 64 bits wide: a batch that straddles 2^32 equals its two halves
+    base = (1 << 32) - 8
+    e = engine.run_pairwise(xy, uid_base=base, **kw)["scores"]
+    e0 = engine.run_pairwise(xy[:1], uid_base=base, **kw)["scores"]
+    e1 = engine.run_pairwise(xy[1:], uid_base=base + 6, **kw)["scores"]
+    assert np.array_equal(e, np.concatenate([e0, e1])) and not np.array_equal(e, a)
     assert np.all(np.isfinite(a)) and np.all(a > 0)
 
 
