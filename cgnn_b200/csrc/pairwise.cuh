@@ -394,6 +394,7 @@ __device__ __forceinline__ void pw_backward_partials(const PwSmem& s, int N, int
     __syncwarp();
     float sd_tot = 0.f;
     for (int q0 = 0; 4 * q0 < NP; q0 += PW_NT) {          // whole warps iterate together (uniform trip count)
+        if (4 * (q0 + (tid & ~31)) >= N) continue;        // this warp's 128 rows are all padding: nothing to add
         const int r0 = 4 * (q0 + tid);
         float x[4], e[4], d[4];
 #pragma unroll
