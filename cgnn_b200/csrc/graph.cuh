@@ -226,12 +226,12 @@ __device__ __forceinline__ void gr_mmd_train_row(const float* __restrict__ Pm, c
     }
 }
 
-// Loss share of one row: sum_j [ k(R_i, B_j) ] over a column source (smem or gmem), fp64 across tiles.
+// Loss share of one row: sum_j [ k(R_i, B_j) ] over columns [c0, c1) of a source (smem or gmem), fp64 across tiles.
 template <int DP, int POL, bool GMEM>
-__device__ __forceinline__ double gr_mmd_eval_row(const float* __restrict__ B, int N, const float2 (&p)[DP / 2]) {
+__device__ __forceinline__ double gr_mmd_eval_cols(const float* __restrict__ B, int c0, int c1, const float2 (&p)[DP / 2]) {
     double tot = 0.0;
-    for (int j0 = 0; j0 < N; j0 += 64) {
-        const int j1 = min(j0 + 64, N);
+    for (int j0 = c0; j0 < c1; j0 += 64) {
+        const int j1 = min(j0 + 64, c1);
         float acc = 0.f;
 #pragma unroll 2
         for (int j = j0; j < j1; ++j) {
@@ -243,6 +243,29 @@ __device__ __forceinline__ double gr_mmd_eval_row(const float* __restrict__ B, i
         tot += double(acc);
     }
     return tot;
+}
+template <int DP, int POL, bool GMEM>
+__device__ __forceinline__ double gr_mmd_eval_row(const float* __restrict__ B, int N, const float2 (&p)[DP / 2]) {
+    return gr_mmd_eval_cols<DP, POL, GMEM>(B, 0, N, p);
+}
+
+// Same for a block of the SAME set as the rows (pred-pred, true-true): the kernel matrix is symmetric, so
+// row block rb takes its diagonal tile once and only "its" half of the other column tiles, doubled - the cyclic
+// assignment J = rb+1 .. rb+npp (mod NB) covers every unordered tile pair exactly once over all row blocks.
+__device__ __forceinline__ int gr_npp(int I, int NB) {
+    return (NB & 1) ? (NB - 1) / 2 : (NB / 2 - 1 + (I < NB / 2 ? 1 : 0));
+}
+template <int DP, int POL, bool GMEM>
+__device__ __forceinline__ double gr_mmd_eval_row_sym(const float* __restrict__ B, int N, int NB, int rb, const float2 (&p)[DP / 2]) {
+    double tot = gr_mmd_eval_cols<DP, POL, GMEM>(B, 32 * rb, min(32 * rb + 32, N), p);
+    const int npp = gr_npp(rb, NB);
+    double off = 0.0;
+    for (int q = 0; q < npp; ++q) {
+        int J = rb + 1 + q;
+        if (J >= NB) J -= NB;
+        off += gr_mmd_eval_cols<DP, POL, GMEM>(B, 32 * J, min(32 * J + 32, N), p);
+    }
+    return tot + 2.0 * off;
 }
 
 // element kk of a hidden vector held as HP/2 register pairs (kk is a compile-time constant after unrolling)
@@ -532,7 +555,7 @@ __global__ void __launch_bounds__(GR_NT, 1) graph_kernel(const GraphArgs a) {
                 gr_load_col_gmem<DP>(T, min(i, N - 1), pf);
 #pragma unroll
                 for (int q = 0; q < DP / 2; ++q) p[q] = make_float2(pf[2 * q], pf[2 * q + 1]);
-                const double v = gr_mmd_eval_row<DP, POL, true>(T, N, p);
+                const double v = gr_mmd_eval_row_sym<DP, POL, true>(T, N, NB, rb, p);
                 if (i < N) part += v;
             }
             const double tt = gr_cluster_sum(part, s.red, warp, lane, cl, csz, crank);
@@ -627,7 +650,7 @@ __global__ void __launch_bounds__(GR_NT, 1) graph_kernel(const GraphArgs a) {
                         gr_load_col_smem<DP>(s.Pm, i, pf);
     #pragma unroll
                         for (int q = 0; q < DP / 2; ++q) p[q] = make_float2(pf[2 * q], pf[2 * q + 1]);
-                        const double v = gr_mmd_eval_row<DP, POL, false>(s.Pm, N, p) - 2.0 * gr_mmd_eval_row<DP, POL, true>(T, N, p);
+                        const double v = gr_mmd_eval_row_sym<DP, POL, false>(s.Pm, N, NB, rb, p) - 2.0 * gr_mmd_eval_row<DP, POL, true>(T, N, p);
                         if (i < N) part += v;
                     }
                     const double sum = gr_cluster_sum(part, s.red, warp, lane, cl, csz, crank);
