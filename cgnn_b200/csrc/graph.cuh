@@ -83,6 +83,7 @@ struct GraphArgs {
     int* counter;
     float *dbg_loss, *dbg_pred, *dbg_dldp, *dbg_grad, *dbg_params;
     // random-feature ("Fourier") MMD, Loss.py:35-56: fast_k = nb_vectors_approx_MMD, 0 = Gaussian-kernel MMD
+    int t_smem;                // 1: the observed matrix of the instance is copied to shared memory (it fits)
     int fast_k;
     const float* wz_ext;       // NULL or [n_inst][epochs][n_var+1][7*fast_k]: the matrix of Loss.py:35-37 per step
 };
@@ -91,9 +92,10 @@ struct GrSmem {
     float* Pm; float* nbuf; float* theta; float* am; float* av; long long* g64; double* red; GraphDesc* desc;
     int nn_pad;
     float* Wc; float* bc; float* coef; long long* et; long long* ep;     // random-feature mode: one bandwidth group
+    float* Ts;                                                           // copy of the observed matrix [NP][DP] (t_smem)
 };
 
-__host__ __device__ inline size_t gr_smem_bytes(int NP, int DP, int n_noise, int p_max, int fast_k = 0) {
+__host__ __device__ inline size_t gr_smem_bytes(int NP, int DP, int n_noise, int p_max, int fast_k = 0, int t_smem = 0) {
     const int nn_pad = (n_noise + 3) & ~3;
     const int pp = (p_max + 3) & ~3;
     size_t b = 0;
@@ -105,6 +107,8 @@ __host__ __device__ inline size_t gr_smem_bytes(int NP, int DP, int n_noise, int
     b += (sizeof(GraphDesc) + 15) & ~size_t(15);
     const int kp = (fast_k + 3) & ~3;
     b += size_t(kp) * (8 + 8 + 4 * DP + 4 + 4);  // et, ep, Wc, bc, coef
+    b = (b + 15) & ~size_t(15);
+    if (t_smem) b += size_t(NP) * DP * 4;        // Ts
     return (b + 15) & ~size_t(15);
 }
 
@@ -195,7 +199,7 @@ __device__ __forceinline__ float gr_sqdist(const float2 (&p)[DP / 2], const floa
 // MMD gradient of one row: tot[c] = sum_j w(P_i,T_j)(P_ic - T_jc) - sum_j w(P_i,P_j)(P_ic - P_jc)   (unscaled)
 // fp32 accumulation in runs of one PT tile + one PP tile (64 evaluations), then a second-level fp32 sum
 // of the (mutually cancelling, hence small) tile pairs.  All column-wise arithmetic is FFMA2/FADD2.
-template <int DP, int POL>
+template <int DP, int POL, bool TS>
 __device__ __forceinline__ void gr_mmd_train_row(const float* __restrict__ Pm, const float* __restrict__ T, int N,
                                                  const float2 (&p)[DP / 2], float2 (&tot)[DP / 2]) {
 #pragma unroll
@@ -208,7 +212,7 @@ __device__ __forceinline__ void gr_mmd_train_row(const float* __restrict__ Pm, c
         for (int j = j0; j < j1; ++j) {
             float t[DP];
             float2 df[DP / 2];
-            gr_load_col_gmem<DP>(T, j, t);
+            if (TS) gr_load_col_smem<DP>(T, j, t); else gr_load_col_gmem<DP>(T, j, t);
             const float2 w = splat2(wsum<POL>(gr_sqdist<DP>(p, t, df)));
 #pragma unroll
             for (int q = 0; q < DP / 2; ++q) acc[q] = ffma2(w, df[q], acc[q]);
@@ -492,7 +496,8 @@ __global__ void __launch_bounds__(GR_NT, 1) graph_kernel(const GraphArgs a) {
         s.ep = reinterpret_cast<long long*>(p);    p += size_t(kp) * 8;
         s.Wc = reinterpret_cast<float*>(p);        p += size_t(kp) * DP * 4;
         s.bc = reinterpret_cast<float*>(p);        p += size_t(kp) * 4;
-        s.coef = reinterpret_cast<float*>(p);
+        s.coef = reinterpret_cast<float*>(p);      p += size_t(kp) * 4;
+        s.Ts = reinterpret_cast<float*>(smem_raw + ((size_t(p - smem_raw) + 15) & ~size_t(15)));
     }
     float* nb = s.nbuf + size_t(warp) * s.nn_pad * 32;
     const int epochs = a.train_epochs + a.test_epochs;
@@ -528,6 +533,11 @@ __global__ void __launch_bounds__(GR_NT, 1) graph_kernel(const GraphArgs a) {
             for (int q = tid; q < int(sizeof(GraphDesc) / 4); q += GR_NT) dst[q] = src[q];
         }
         for (int q = tid; q < a.NP * DP; q += GR_NT) s.Pm[q] = 0.f;
+        if (a.t_smem) {
+            const float4* src = reinterpret_cast<const float4*>(T);
+            float4* dst = reinterpret_cast<float4*>(s.Ts);
+            for (int q = tid; q < a.NP * DP / 4; q += GR_NT) dst[q] = __ldg(src + q);
+        }
         __syncthreads();
         const int P = s.desc->n_params, PPAD = s.desc->n_params_pad;
         for (int q = tid; q < pp; q += GR_NT) { s.theta[q] = 0.f; s.am[q] = 0.f; s.av[q] = 0.f; s.g64[q] = 0; }
@@ -650,7 +660,8 @@ __global__ void __launch_bounds__(GR_NT, 1) graph_kernel(const GraphArgs a) {
                         gr_load_col_smem<DP>(s.Pm, i, pf);
     #pragma unroll
                         for (int q = 0; q < DP / 2; ++q) p[q] = make_float2(pf[2 * q], pf[2 * q + 1]);
-                        const double v = gr_mmd_eval_row_sym<DP, POL, false>(s.Pm, N, NB, rb, p) - 2.0 * gr_mmd_eval_row<DP, POL, true>(T, N, p);
+                        const double v = gr_mmd_eval_row_sym<DP, POL, false>(s.Pm, N, NB, rb, p) -
+                                         2.0 * (a.t_smem ? gr_mmd_eval_row<DP, POL, false>(s.Ts, N, p) : gr_mmd_eval_row<DP, POL, true>(T, N, p));
                         if (i < N) part += v;
                     }
                     const double sum = gr_cluster_sum(part, s.red, warp, lane, cl, csz, crank);
@@ -674,7 +685,8 @@ __global__ void __launch_bounds__(GR_NT, 1) graph_kernel(const GraphArgs a) {
                         gr_load_col_smem<DP>(s.Pm, i, pf);
     #pragma unroll
                         for (int q = 0; q < DP / 2; ++q) p[q] = make_float2(pf[2 * q], pf[2 * q + 1]);
-                        gr_mmd_train_row<DP, POL>(s.Pm, T, N, p, tot);
+                        if (a.t_smem) gr_mmd_train_row<DP, POL, true>(s.Pm, s.Ts, N, p, tot);
+                        else gr_mmd_train_row<DP, POL, false>(s.Pm, T, N, p, tot);
     #pragma unroll
                         for (int q = 0; q < DP / 2; ++q) {
                             gl[2 * q] = (i < N) ? tot[q].x * scale : 0.f;

@@ -213,7 +213,11 @@ static int run_graph_impl(cgnn_ctx* ctx, const cgnn_hparams* hp, const float* da
     a.lr = hp->learning_rate; a.init_std = hp->init_std; a.ld_params = ld_params;
     a.key = make_uint2((unsigned int)(hp->seed & 0xffffffffu), (unsigned int)(hp->seed >> 32));
 
-    const size_t smem = gr_smem_bytes(NP, DP, n_noise, p_pad_max, a.fast_k);
+    // the observed matrix goes to shared memory too when everything still fits one SM (decided by the instance
+    // shape only; the arithmetic is the same either way)
+    const size_t smem_ts = gr_smem_bytes(NP, DP, n_noise, p_pad_max, a.fast_k, 1);
+    a.t_smem = (a.fast_k == 0 && smem_ts <= size_t(ctx->prop.sharedMemPerBlockOptin)) ? 1 : 0;
+    const size_t smem = a.t_smem ? smem_ts : gr_smem_bytes(NP, DP, n_noise, p_pad_max, a.fast_k);
     if (smem > size_t(ctx->prop.sharedMemPerBlockOptin))
         return fail(ctx, CGNN_ERR_LIMIT, "graph instance needs %zu B of shared memory (rows %d x cols %d, %d noise columns, %d parameters); "
                     "device allows %zu", smem, n_rows, DP, n_noise, p_max, size_t(ctx->prop.sharedMemPerBlockOptin));
