@@ -84,6 +84,7 @@ struct GraphArgs {
     float *dbg_loss, *dbg_pred, *dbg_dldp, *dbg_grad, *dbg_params;
     // random-feature ("Fourier") MMD, Loss.py:35-56: fast_k = nb_vectors_approx_MMD, 0 = Gaussian-kernel MMD
     int t_smem;                // 1: the observed matrix of the instance is copied to shared memory (it fits)
+    int t_ring;                // 1: it does not fit and is streamed through the warps' idle noise buffers (gr_mmd_train_row_ring)
     int fast_k;
     const float* wz_ext;       // NULL or [n_inst][epochs][n_var+1][7*fast_k]: the matrix of Loss.py:35-37 per step
 };
@@ -228,6 +229,104 @@ __device__ __forceinline__ void gr_mmd_train_row(const float* __restrict__ Pm, c
 #pragma unroll
         for (int q = 0; q < DP / 2; ++q) tot[q] = fadd2(tot[q], acc[q]);
     }
+}
+
+// ---- observed matrix streamed through a per-warp ring (shapes whose observed matrix does not fit shared memory) --
+// The warp's noise buffer is idle while the warp walks the observed rows, and it holds at least 32 rows whenever
+// nn_pad >= DP: two halves of GR_RING_H rows, filled with cp.async one half ahead of the arithmetic, replace
+// the L1/L2 round trip of every row by a shared-memory broadcast read.  Same order of operations as
+// gr_mmd_train_row / gr_mmd_eval_cols.
+constexpr int GR_RING_H = 16;
+
+__device__ __forceinline__ void gr_cp_async16(void* dst_smem, const void* src) {
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((unsigned)__cvta_generic_to_shared(dst_smem)), "l"(src) : "memory");
+}
+// chunk c = rows [c*H, c*H + H) of T (padded to NP rows, so a whole chunk is always readable) -> half c & 1; one group
+template <int DP>
+__device__ __forceinline__ void gr_ring_issue(const float* __restrict__ T, float* ring, int c, int n_chunks, int lane) {
+    if (c < n_chunks) {
+        const float4* src = reinterpret_cast<const float4*>(T + size_t(c) * GR_RING_H * DP);
+        float4* dst = reinterpret_cast<float4*>(ring + (c & 1) * GR_RING_H * DP);
+#pragma unroll
+        for (int q = lane; q < GR_RING_H * DP / 4; q += 32) gr_cp_async16(dst + q, src + q);
+    }
+    asm volatile("cp.async.commit_group;" ::: "memory");
+}
+__device__ __forceinline__ void gr_ring_wait() {            // everything but the newest group has landed, warp-wide
+    asm volatile("cp.async.wait_group 1;" ::: "memory");
+    __syncwarp();
+}
+
+template <int DP, int POL>
+__device__ __forceinline__ void gr_mmd_train_row_ring(const float* __restrict__ Pm, const float* __restrict__ T, float* ring, int N,
+                                                      int lane, const float2 (&p)[DP / 2], float2 (&tot)[DP / 2]) {
+    const int n_chunks = (N + GR_RING_H - 1) / GR_RING_H;
+#pragma unroll
+    for (int q = 0; q < DP / 2; ++q) tot[q] = make_float2(0.f, 0.f);
+    gr_ring_issue<DP>(T, ring, 0, n_chunks, lane);
+    for (int j0 = 0; j0 < N; j0 += 32) {
+        const int j1 = min(j0 + 32, N);
+        float2 acc[DP / 2];
+#pragma unroll
+        for (int q = 0; q < DP / 2; ++q) acc[q] = make_float2(0.f, 0.f);
+        for (int c = j0 / GR_RING_H; c * GR_RING_H < j1; ++c) {
+            gr_ring_issue<DP>(T, ring, c + 1, n_chunks, lane);
+            gr_ring_wait();
+            const float* B = ring + (c & 1) * GR_RING_H * DP;
+            const int n = min(GR_RING_H, j1 - c * GR_RING_H);
+            for (int j = 0; j < n; ++j) {
+                float t[DP];
+                float2 df[DP / 2];
+                gr_load_col_smem<DP>(B, j, t);
+                const float2 w = splat2(wsum<POL>(gr_sqdist<DP>(p, t, df)));
+#pragma unroll
+                for (int q = 0; q < DP / 2; ++q) acc[q] = ffma2(w, df[q], acc[q]);
+            }
+            __syncwarp();                                   // the half may be refilled two chunks later
+        }
+        for (int j = j0; j < j1; ++j) {
+            float t[DP];
+            float2 df[DP / 2];
+            gr_load_col_smem<DP>(Pm, j, t);
+            const float2 w = splat2(-wsum<POL>(gr_sqdist<DP>(p, t, df)));
+#pragma unroll
+            for (int q = 0; q < DP / 2; ++q) acc[q] = ffma2(w, df[q], acc[q]);
+        }
+#pragma unroll
+        for (int q = 0; q < DP / 2; ++q) tot[q] = fadd2(tot[q], acc[q]);
+    }
+    asm volatile("cp.async.wait_group 0;" ::: "memory");
+    __syncwarp();
+}
+
+// sum_j k(R_i, T_j) over all N observed rows, fp32 runs of 64 then fp64 (as gr_mmd_eval_cols)
+template <int DP, int POL>
+__device__ __forceinline__ double gr_mmd_eval_row_ring(const float* __restrict__ T, float* ring, int N, int lane, const float2 (&p)[DP / 2]) {
+    const int n_chunks = (N + GR_RING_H - 1) / GR_RING_H;
+    double tot = 0.0;
+    gr_ring_issue<DP>(T, ring, 0, n_chunks, lane);
+    for (int j0 = 0; j0 < N; j0 += 64) {
+        const int j1 = min(j0 + 64, N);
+        float acc = 0.f;
+        for (int c = j0 / GR_RING_H; c * GR_RING_H < j1; ++c) {
+            gr_ring_issue<DP>(T, ring, c + 1, n_chunks, lane);
+            gr_ring_wait();
+            const float* B = ring + (c & 1) * GR_RING_H * DP;
+            const int n = min(GR_RING_H, j1 - c * GR_RING_H);
+#pragma unroll 2
+            for (int j = 0; j < n; ++j) {
+                float t[DP];
+                float2 df[DP / 2];
+                gr_load_col_smem<DP>(B, j, t);
+                acc += ksum<POL>(gr_sqdist<DP>(p, t, df));
+            }
+            __syncwarp();
+        }
+        tot += double(acc);
+    }
+    asm volatile("cp.async.wait_group 0;" ::: "memory");
+    __syncwarp();
+    return tot;
 }
 
 // Loss share of one row: sum_j [ k(R_i, B_j) ] over columns [c0, c1) of a source (smem or gmem), fp64 across tiles.
@@ -661,7 +760,8 @@ __global__ void __launch_bounds__(GR_NT, 1) graph_kernel(const GraphArgs a) {
     #pragma unroll
                         for (int q = 0; q < DP / 2; ++q) p[q] = make_float2(pf[2 * q], pf[2 * q + 1]);
                         const double v = gr_mmd_eval_row_sym<DP, POL, false>(s.Pm, N, NB, rb, p) -
-                                         2.0 * (a.t_smem ? gr_mmd_eval_row<DP, POL, false>(s.Ts, N, p) : gr_mmd_eval_row<DP, POL, true>(T, N, p));
+                                         2.0 * (a.t_smem ? gr_mmd_eval_row<DP, POL, false>(s.Ts, N, p)
+                                                : a.t_ring ? gr_mmd_eval_row_ring<DP, POL>(T, nb, N, lane, p) : gr_mmd_eval_row<DP, POL, true>(T, N, p));
                         if (i < N) part += v;
                     }
                     const double sum = gr_cluster_sum(part, s.red, warp, lane, cl, csz, crank);
@@ -686,6 +786,7 @@ __global__ void __launch_bounds__(GR_NT, 1) graph_kernel(const GraphArgs a) {
     #pragma unroll
                         for (int q = 0; q < DP / 2; ++q) p[q] = make_float2(pf[2 * q], pf[2 * q + 1]);
                         if (a.t_smem) gr_mmd_train_row<DP, POL, true>(s.Pm, s.Ts, N, p, tot);
+                        else if (a.t_ring) gr_mmd_train_row_ring<DP, POL>(s.Pm, T, nb, N, lane, p, tot);
                         else gr_mmd_train_row<DP, POL, false>(s.Pm, T, N, p, tot);
     #pragma unroll
                         for (int q = 0; q < DP / 2; ++q) {

@@ -218,6 +218,7 @@ static int run_graph_impl(cgnn_ctx* ctx, const cgnn_hparams* hp, const float* da
     const size_t smem_ts = gr_smem_bytes(NP, DP, n_noise, p_pad_max, a.fast_k, 1);
     a.t_smem = (a.fast_k == 0 && smem_ts <= size_t(ctx->prop.sharedMemPerBlockOptin)) ? 1 : 0;
     const size_t smem = a.t_smem ? smem_ts : gr_smem_bytes(NP, DP, n_noise, p_pad_max, a.fast_k);
+    a.t_ring = (!a.t_smem && a.fast_k == 0 && ((n_noise + 3) & ~3) >= DP) ? 1 : 0;
     if (smem > size_t(ctx->prop.sharedMemPerBlockOptin))
         return fail(ctx, CGNN_ERR_LIMIT, "graph instance needs %zu B of shared memory (rows %d x cols %d, %d noise columns, %d parameters); "
                     "device allows %zu", smem, n_rows, DP, n_noise, p_max, size_t(ctx->prop.sharedMemPerBlockOptin));

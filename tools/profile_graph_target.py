@@ -1,5 +1,6 @@
 """Small fixed workload for ncu: one launch of the graph instance kernel on the bundled 22-variable
-example (148 instances = one wave).  Usage: python tools/profile_graph_target.py [pol] [train] [test]"""
+example (148 instances = one wave), or with shape=c5 on the synthetic 20-variable, 1500-row shape of
+BASELINE configs[5].  Usage: python tools/profile_graph_target.py [pol] [train] [test] [c2|c5]"""
 import os, sys
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import numpy as np, pandas as pd
@@ -9,10 +10,19 @@ from cgnn_b200.utils.scaling import scale
 pol = int(sys.argv[1]) if len(sys.argv) > 1 else 3
 train = int(sys.argv[2]) if len(sys.argv) > 2 else 8
 test = int(sys.argv[3]) if len(sys.argv) > 3 else 4
+shape = sys.argv[4] if len(sys.argv) > 4 else "c2"
 EX = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "examples")
 data = pd.read_csv(os.path.join(EX, "Example_graph_numdata.csv"))
 dag = DirectedGraph(pd.read_csv(os.path.join(EX, "Example_graph_target.csv")))
 plan = build_plan(dag, columns=list(data.columns))
+if shape == "c5":
+    from cgnn_b200 import synth
+    Xs, edges = synth.make_dag_dataset(20, 1500, 3)
+    data = pd.DataFrame(Xs, columns=["V%d" % k for k in range(20)])
+    dag = DirectedGraph()
+    for a, b in edges:
+        dag.add("V%d" % a, "V%d" % b, 1.0)
+    plan = build_plan(dag, columns=list(data.columns))
 X = scale(data.values).astype(np.float32)
 eng = Engine(0)
 for rep in range(2):
