@@ -186,7 +186,7 @@ def workload_config(args, world):
                            "final all_gather of scores" % world,
             "l2_policy": "working set lives in shared memory for the whole launch (HBM/L2 touched once per instance); "
                          "every step uses fresh pairs, so nothing is served from a previous step's cache",
-            "exp_policy": args.exp_policy}
+            "exp_policy": 3 if args.exp_policy < 0 else args.exp_policy}
 
 
 def main():
@@ -331,7 +331,8 @@ def main():
                             "write 0 (profiles/r1_pairwise_pol3_trio_ncu_full.txt) - the working set lives in shared memory",
             "note": "algorithmic count = 7 exp per kernel evaluation (SURVEY 8d); exp_policy p issues 7/5/4/3 MUFU per "
                     "evaluation for p=0/1/2/3 (the others come from exact power relations between the bandwidths), so "
-                    "frac can exceed 1.0; ncu pipe utilisation of this kernel: XU 80 %, FMA 68 %, issue slots 84 %"}
+                    "frac can exceed 1.0; ncu pipe utilisation of this kernel (policy 3, "
+                    "profiles/r1_pairwise_pol3_packed_ncu_full.txt): XU 85 %, issue slots 59 %"}
 
     out = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
            "warmup": args.warmup, "ms_per_step": dev_ms / args.steps, "higher_is_better": True, "scaling": "weak",

@@ -233,14 +233,15 @@ static int run_pairwise_impl(cgnn_ctx* ctx, const cgnn_hparams* hp, const float*
     if (smem > size_t(ctx->prop.sharedMemPerBlockOptin))
         return fail(ctx, CGNN_ERR_LIMIT, "instance needs %zu B of shared memory, device allows %zu", smem,
                     size_t(ctx->prop.sharedMemPerBlockOptin));
-    int per_sm = pairwise_occupancy(hp->exp_policy, smem);
+    const int pol = hp->exp_policy < 0 ? CGNN_EXP_POLICY_PAIRWISE : hp->exp_policy;
+    int per_sm = pairwise_occupancy(pol, smem);
     if (per_sm < 1) return fail(ctx, CGNN_ERR_CUDA, "pairwise kernel cannot be resident (smem %zu B)", smem);
     ctx->pw_ctas_per_sm = per_sm;
     const int grid = std::min(n_inst, per_sm * ctx->prop.multiProcessorCount);
 
     CU(cudaEventRecord(ctx->ev0, ctx->stream));
     cudaError_t le = cudaErrorInvalidValue;
-    switch (hp->exp_policy) {
+    switch (pol) {
         case 0: le = launch_pairwise<0>(a, grid, smem, ctx->stream); break;
         case 1: le = launch_pairwise<1>(a, grid, smem, ctx->stream); break;
         case 2: le = launch_pairwise<2>(a, grid, smem, ctx->stream); break;
@@ -370,7 +371,7 @@ extern "C" int cgnn_b200_run_pairwise_noalloc(int device, void* stream, const cg
     if (!hp || !d_xy || !d_scores) return na_fail(errbuf, errbuf_len, CGNN_ERR_ARG, "hparams, d_xy and d_scores must not be NULL");
     if (hp->h_layer_dim < 1 || hp->h_layer_dim > CGNN_MAX_H)
         return na_fail(errbuf, errbuf_len, CGNN_ERR_LIMIT, "h_layer_dim=%d outside [1,%d]", hp->h_layer_dim, CGNN_MAX_H);
-    if (hp->train_epochs < 0 || hp->test_epochs < 0 || hp->exp_policy < 0 || hp->exp_policy > 3)
+    if (hp->train_epochs < 0 || hp->test_epochs < 0 || hp->exp_policy < CGNN_EXP_POLICY_AUTO || hp->exp_policy > 3)
         return na_fail(errbuf, errbuf_len, CGNN_ERR_ARG, "bad epoch count or exp_policy");
     if (hp->fast_mmd_vectors < 0 || hp->fast_mmd_vectors > CGNN_MAX_FAST_VECTORS)
         return na_fail(errbuf, errbuf_len, CGNN_ERR_LIMIT, "fast_mmd_vectors=%d outside [0,%d]", hp->fast_mmd_vectors, CGNN_MAX_FAST_VECTORS);
@@ -417,11 +418,12 @@ extern "C" int cgnn_b200_run_pairwise_noalloc(int device, void* stream, const cg
 
     const size_t smem = pw_smem_bytes(a.np_max, a.h, a.fast_k);
     if (smem > size_t(smem_optin)) return na_fail(errbuf, errbuf_len, CGNN_ERR_LIMIT, "instance needs %zu B of shared memory", smem);
-    const int per_sm = pairwise_occupancy(hp->exp_policy, smem);
+    const int pol = hp->exp_policy < 0 ? CGNN_EXP_POLICY_PAIRWISE : hp->exp_policy;
+    const int per_sm = pairwise_occupancy(pol, smem);
     if (per_sm < 1) return na_fail(errbuf, errbuf_len, CGNN_ERR_CUDA, "pairwise kernel cannot be resident");
     const int grid = std::min(n_inst, per_sm * n_sm);
     cudaError_t le = cudaErrorInvalidValue;
-    switch (hp->exp_policy) {
+    switch (pol) {
         case 0: le = launch_pairwise<0>(a, grid, smem, st); break;
         case 1: le = launch_pairwise<1>(a, grid, smem, st); break;
         case 2: le = launch_pairwise<2>(a, grid, smem, st); break;

@@ -222,6 +222,7 @@ static int run_graph_impl(cgnn_ctx* ctx, const cgnn_hparams* hp, const float* da
     if (smem > size_t(ctx->prop.sharedMemPerBlockOptin))
         return fail(ctx, CGNN_ERR_LIMIT, "graph instance needs %zu B of shared memory (rows %d x cols %d, %d noise columns, %d parameters); "
                     "device allows %zu", smem, n_rows, DP, n_noise, p_max, size_t(ctx->prop.sharedMemPerBlockOptin));
+    const int pol = hp->exp_policy < 0 ? CGNN_EXP_POLICY_GRAPH : hp->exp_policy;
     // ---- CTAs per instance: a cluster when the batch cannot fill the GPU with one CTA per instance ----------
     const int NB = NP / 32;
     int best_csz = 1, best_slots = std::max(1, ctx->prop.multiProcessorCount);
@@ -234,7 +235,7 @@ static int run_graph_impl(cgnn_ctx* ctx, const cgnn_hparams* hp, const float* da
         if (dbg_host && csz > 1) break;                              // the parity probe runs on one CTA
         if (hp->graph_cluster > 0 && csz != hp->graph_cluster) continue;
         int slots = 0;
-        if (launch_graph(DP, HP, hp->exp_policy, a, -1, csz, smem, ctx->stream, &slots) != cudaSuccess || slots < 1) {
+        if (launch_graph(DP, HP, pol, a, -1, csz, smem, ctx->stream, &slots) != cudaSuccess || slots < 1) {
             cudaGetLastError();
             continue;
         }
@@ -248,7 +249,7 @@ static int run_graph_impl(cgnn_ctx* ctx, const cgnn_hparams* hp, const float* da
     ctx->last_cluster = best_csz;
 
     CU(cudaEventRecord(ctx->ev0, ctx->stream));
-    cudaError_t le = launch_graph(DP, HP, hp->exp_policy, a, n_clusters, best_csz, smem, ctx->stream, nullptr);
+    cudaError_t le = launch_graph(DP, HP, pol, a, n_clusters, best_csz, smem, ctx->stream, nullptr);
     if (le != cudaSuccess) return fail(ctx, CGNN_ERR_CUDA, "graph kernel launch: %s", cudaGetErrorString(le));
     CU(cudaEventRecord(ctx->ev1, ctx->stream));
     ctx->last_launches = 2;

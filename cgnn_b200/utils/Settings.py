@@ -4,7 +4,7 @@ time and overridable per call through **kwargs of the same (lower-case) names, a
 does (GNN.py:45-48; CGNN.py:48-51,208-209).
 
 Engine-only additions: `seed` (the reference is unseeded), `exp_policy` (how the CUDA kernel
-produces the 7 Gaussian kernel values, see include/cgnn_b200.h), `verbose` and `work_stealing`
+produces the 7 Gaussian kernel values, see include/cgnn_b200.h; -1 = the fastest per path), `verbose` and `work_stealing`
 (chunked dynamic schedule over GPUs / ranks, cgnn_b200/runtime.py).
 `NB_JOBS` is accepted and ignored (no process pool: one launch scores the whole batch);
 `NB_GPU`/`GPU_OFFSET` select which GPUs a single process drives.
@@ -18,7 +18,7 @@ _REFERENCE_DEFAULTS = (
     ("h_layer_dim", 20), ("train_epochs", 1000), ("test_epochs", 500),
     ("use_Fast_MMD", False), ("nb_vectors_approx_MMD", 100), ("complexity_graph_param", 0.00005),
 )
-_ENGINE_DEFAULTS = (("seed", 0), ("exp_policy", 3), ("verbose", True), ("work_stealing", False))
+_ENGINE_DEFAULTS = (("seed", 0), ("exp_policy", -1), ("verbose", True), ("work_stealing", False))
 
 
 class EngineSettings(object):

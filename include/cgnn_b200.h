@@ -49,6 +49,10 @@ typedef enum cgnn_status {
 
 typedef struct cgnn_ctx cgnn_ctx;
 
+#define CGNN_EXP_POLICY_AUTO     (-1)
+#define CGNN_EXP_POLICY_PAIRWISE 3
+#define CGNN_EXP_POLICY_GRAPH    1
+
 /* Hyper-parameters.  Mirrors the knobs of Code/cgnn/utils/Settings.py:26-41 that reach the
  * device code, plus the engine's own (seed, exp_policy, trace_every). */
 typedef struct cgnn_hparams {
@@ -60,7 +64,10 @@ typedef struct cgnn_hparams {
     int   exp_policy;         /* how the 7 Gaussian kernels of one pair evaluation are produced (all within the
                                  1e-5 parity bound, measured 2e-6): 0 = seven MUFU ex2; 1 = five (gamma 0.5, 1 by
                                  squaring gamma 0.25); 2 = four (+ gamma 0.05 = 10th power of 0.005);
-                                 3 = three (+ gamma 5 = 5th power of gamma 1) */
+                                 3 = three (+ gamma 5 = 5th power of gamma 1);
+                                 CGNN_EXP_POLICY_AUTO (-1) = the fastest measured per path: 3 on the pairwise path
+                                 (bound by the MUFU pipe), 1 on the graph path (bound by the FMA pipe, where an
+                                 ex2 is cheaper than the multiplies that replace it) */
     int   trace_every;        /* >0: also compute the (pre-update) training loss on every trace_every-th
                                  train step into loss_trace (GNN.py:98-102 prints every 100th); 0 = never */
     int   fast_mmd_vectors;   /* 0: Gaussian-kernel MMD (SETTINGS.use_Fast_MMD = False).  k > 0: the random-feature loss
