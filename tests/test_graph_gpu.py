@@ -84,11 +84,12 @@ def test_graph_step_debug_matches_oracle(engine, n, n_var, h, conf, pol):
         assert relerr(got["params"][s], ref["params"][s]) < 1e-4
 
 
-def test_graph_full_size_step(engine):
-    """The shapes of the bundled graph example: 500 rows, 22 variables, h = 20."""
+@pytest.mark.parametrize("n,n_var,h", [(500, 22, 20), (1500, 20, 20)])
+def test_graph_full_size_step(engine, n, n_var, h):
+    """The shapes of the bundled graph example (500 rows, 22 variables, h = 20: both matrices in shared memory) and
+    of BASELINE configs[4] (1500 rows, 20 variables: the observed matrix streamed through the per-warp ring)."""
     from cgnn_b200.plan import build_plan, n_params
     from oracle import cgnn as oc
-    n, n_var, h = 500, 22, 20
     g = random_dag(n_var, 2, 5)
     plan = build_plan(g)
     data = make_data(n, n_var, 3)
@@ -208,6 +209,18 @@ def test_cluster_sizes_agree(engine):
         assert np.array_equal(r["params"], base["params"]), "cluster size %d changed the trained parameters" % c
         np.testing.assert_allclose(r["scores"], base["scores"], rtol=1e-6)
         np.testing.assert_allclose(r["trace"], base["trace"], rtol=1e-6, equal_nan=True)
+    # 20 variables x 1500 rows: the observed matrix no longer fits shared memory and is streamed through the
+    # per-warp cp.async ring - the same property must hold on that code path
+    g20 = random_dag(20, 3, 5)
+    plan20 = build_plan(g20)
+    data20 = make_data(1500, 20, 6)
+    kw20 = dict(n_runs=2, h_layer_dim=20, train_epochs=4, test_epochs=2, seed=3, want_params=True)
+    base20 = engine.run_graph(data20, [plan20], graph_cluster=1, **kw20)
+    for c in (2, 3):
+        r = engine.run_graph(data20, [plan20], graph_cluster=c, **kw20)
+        assert engine.last_graph_cluster == c
+        assert np.array_equal(r["params"], base20["params"]), "cluster size %d changed the trained parameters (ring path)" % c
+        np.testing.assert_allclose(r["scores"], base20["scores"], rtol=1e-6)
     # automatic choice: few long instances -> a cluster; many instances -> one CTA each
     engine.run_graph(make_data(1500, n_var, 1), [plan], n_runs=4, h_layer_dim=10, train_epochs=2, test_epochs=1)
     assert engine.last_graph_cluster >= 2
