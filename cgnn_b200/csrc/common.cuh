@@ -207,11 +207,14 @@ __device__ __forceinline__ float2 splat2(float w) { return make_float2(w, w); }
 // ---------------------------------------------------------------------------------------------
 __device__ __forceinline__ float2 ex2f2(float2 x) { return make_float2(ex2f(x.x), ex2f(x.y)); }
 
-template <int POL>
+// FAR: the caller guarantees Dp > CGNN_FAR_DP for both halves; the gamma = 50 kernel is then below 5e-11 and left out.
+#define CGNN_FAR_DP 0.2f          /* primed units: D > 0.5545; 50 e^{-50 D} / (0.005 e^{-0.005 D}) < 1e-8 */
+
+template <int POL, bool FAR = false>
 __device__ __forceinline__ float2 wsum_p2(float2 Dp) {
     const float2 q = ex2f2(fmul2(Dp, splat2(-0.02f)));
     const float2 p = ex2f2(make_float2(-Dp.x, -Dp.y));
-    float2 w = ex2f2(ffma2(Dp, splat2(-200.0f), splat2(CGNN_LOG2_50)));
+    float2 w = FAR ? make_float2(0.f, 0.f) : ex2f2(ffma2(Dp, splat2(-200.0f), splat2(CGNN_LOG2_50)));
     if (POL >= 2) {
         const float2 q2 = fmul2(q, q), q4 = fmul2(q2, q2), q8 = fmul2(q4, q4);
         w = ffma2(ffma2(splat2(G1), fmul2(q8, q), splat2(G0)), q, w);
@@ -232,11 +235,11 @@ __device__ __forceinline__ float2 wsum_p2(float2 Dp) {
     return w;
 }
 
-template <int POL>
+template <int POL, bool FAR = false>
 __device__ __forceinline__ float2 ksum_p2(float2 Dp) {
     const float2 q = ex2f2(fmul2(Dp, splat2(-0.02f)));
     const float2 p = ex2f2(make_float2(-Dp.x, -Dp.y));
-    float2 s = ex2f2(fmul2(Dp, splat2(-200.0f)));
+    float2 s = FAR ? make_float2(0.f, 0.f) : ex2f2(fmul2(Dp, splat2(-200.0f)));
     if (POL >= 2) { const float2 q2 = fmul2(q, q), q4 = fmul2(q2, q2), q5 = fmul2(q4, q); s = fadd2(s, ffma2(q5, q5, q)); }
     else s = fadd2(s, fadd2(q, ex2f2(fmul2(Dp, splat2(-0.2f)))));
     if (POL >= 1) {

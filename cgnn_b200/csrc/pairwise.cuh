@@ -18,6 +18,13 @@
 //   xs[NP], es[NP], yh[NP]  unscaled cause, current noise and generated value (generator phases)
 //   g64[NP] int64           fixed-point accumulator of dLoss/d yhat (primed, unscaled)
 //   padded rows hold x = 1e15 so that every kernel value against them is exactly 0.
+// Rows sit in Qd (and g64) in ascending order of the CAUSE coordinate, rank[i] = sorted position of row i; the
+// per-row generator arrays xs/es/yh stay in the caller's order, so noise streams and outputs are keyed by the
+// caller's row index.  The cause column is copied into the generated pair, so (x_i - x_j)^2 of any two rows
+// never changes during training: a tile pair whose x ranges are further apart than CGNN_FAR_DP (primed units)
+// cannot see the gamma = 50 kernel (50 e^{-50 D} < 5e-11 against the other six, < 1e-8 relative) and is walked
+// with two instead of three MUFU ex2 per evaluation ("far" variant, about 58 % of the tile pairs of a
+// standardised pair).
 //
 // MMD mapping ("trio"): for an unordered pair of DIFFERENT tiles (I, J), lane l owns row i = 32 I + l
 // and meets column j = 32 J + ((l+s)&31) at step s.  The three kernel evaluations that involve the
@@ -71,7 +78,7 @@ struct PairwiseArgs {
 };
 
 struct PwSmem {
-    float4* Qd; float* xs; float* es; float* yh; long long* g64;
+    float4* Qd; float* xs; float* es; float* yh; long long* g64; unsigned short* rank;
     float* theta; float* am; float* av; float* part; double* red;
     int part_stride;
     float4* feat; long long* et; long long* ep;      // Fourier mode only: features (wx/S, wy/S, phase, coef), column sums
@@ -86,6 +93,7 @@ __host__ __device__ inline size_t pw_smem_bytes(int np_max, int h, int fast_k = 
     b += size_t(np_max) * 8;                     // g64
     b += size_t(PW_NW + 4) * 8;                  // red[], TT, beta1^t, beta2^t, lr_t
     b += size_t(np_max) * 4 * 3;                 // xs, es, yh
+    b += size_t(np_max) * 2;                     // rank
     b += size_t(Pp) * 4 * 3;                     // theta, m, v
     b += size_t(PW_NW) * (nchunk * 32 + 4) * 4;  // per-warp partial gradient sums
     b = (b + 15) & ~size_t(15);
@@ -107,7 +115,7 @@ __device__ __forceinline__ int pw_npp(int I, int NB) {
 // Off-diagonal tile pair, gradient form.  tile = &Qd[64 J + lane].  Returns the row-side sum for row i;
 // colsum receives the total for column 32 J + lane (both in primed units, unscaled).  Two steps of the
 // walk are evaluated together: their six kernel evaluations run as three FP32x2-packed chains.
-template <int POL>
+template <int POL, bool FAR>
 __device__ __forceinline__ float trio_train(float xi, float yi, float yhi, const float4* __restrict__ tile, int lane,
                                             float& colsum) {
     float2 ra = make_float2(0.f, 0.f);
@@ -121,9 +129,9 @@ __device__ __forceinline__ float trio_train(float xi, float yi, float yhi, const
         const float2 a = make_float2(yhi - c0.z, yhi - c1.z);      // PP(i,j):  yhat_i - yhat_j
         const float2 b = make_float2(yhi - c0.y, yhi - c1.y);      // PT(i,j):  yhat_i - y_j
         const float2 d = make_float2(c0.z - yi, c1.z - yi);        // PT(j,i):  yhat_j - y_i
-        const float2 wpp = wsum_p2<POL>(make_float2(fmaf(a.x, a.x, e0), fmaf(a.y, a.y, e1)));
-        const float2 w1 = wsum_p2<POL>(make_float2(fmaf(b.x, b.x, e0), fmaf(b.y, b.y, e1)));
-        const float2 w2 = wsum_p2<POL>(make_float2(fmaf(d.x, d.x, e0), fmaf(d.y, d.y, e1)));
+        const float2 wpp = wsum_p2<POL, FAR>(make_float2(fmaf(a.x, a.x, e0), fmaf(a.y, a.y, e1)));
+        const float2 w1 = wsum_p2<POL, FAR>(make_float2(fmaf(b.x, b.x, e0), fmaf(b.y, b.y, e1)));
+        const float2 w2 = wsum_p2<POL, FAR>(make_float2(fmaf(d.x, d.x, e0), fmaf(d.y, d.y, e1)));
         const float2 wa = fmul2(wpp, a);
         ra = fsub2(ffma2(w1, b, ra), wa);
         const float2 cc = ffma2(w2, d, wa);
@@ -151,7 +159,7 @@ __device__ __forceinline__ float duo_train(float xi, float yhi, const float4* __
 }
 
 // Loss forms: kPP - kPT(i,j) - kPT(j,i) per unordered pair (to be doubled), kPP - 2 kPT per ordered pair.
-template <int POL>
+template <int POL, bool FAR>
 __device__ __forceinline__ float trio_eval(float xi, float yi, float yhi, const float4* __restrict__ tile) {
     float2 acc = make_float2(0.f, 0.f);
     CGNN_UNROLL(CGNN_TRIO_UNROLL)
@@ -160,9 +168,9 @@ __device__ __forceinline__ float trio_eval(float xi, float yi, float yhi, const 
         const float dx0 = xi - c0.x, dx1 = xi - c1.x;
         const float e0 = dx0 * dx0, e1 = dx1 * dx1;
         const float a0 = yhi - c0.z, a1 = yhi - c1.z, b0 = yhi - c0.y, b1 = yhi - c1.y, d0 = c0.z - yi, d1 = c1.z - yi;
-        const float2 kpp = ksum_p2<POL>(make_float2(fmaf(a0, a0, e0), fmaf(a1, a1, e1)));
-        const float2 k1 = ksum_p2<POL>(make_float2(fmaf(b0, b0, e0), fmaf(b1, b1, e1)));
-        const float2 k2 = ksum_p2<POL>(make_float2(fmaf(d0, d0, e0), fmaf(d1, d1, e1)));
+        const float2 kpp = ksum_p2<POL, FAR>(make_float2(fmaf(a0, a0, e0), fmaf(a1, a1, e1)));
+        const float2 k1 = ksum_p2<POL, FAR>(make_float2(fmaf(b0, b0, e0), fmaf(b1, b1, e1)));
+        const float2 k2 = ksum_p2<POL, FAR>(make_float2(fmaf(d0, d0, e0), fmaf(d1, d1, e1)));
         acc = fadd2(acc, fsub2(kpp, fadd2(k1, k2)));
     }
     return acc.x + acc.y;
@@ -211,12 +219,16 @@ __device__ double mmd_pass(const float4* __restrict__ Qd, long long* g64, int N,
                 int J = I + q;
                 if (J >= NB) J -= NB;
                 const float4* tile = Qd + 64 * J + lane;
+                // rows are sorted by x: the gap between the x ranges of the two tiles bounds every (x_i - x_j)^2
+                const float gap = (J > I) ? Qd[64 * J].x - Qd[64 * I + 31].x : Qd[64 * I].x - Qd[64 * J + 31].x;
+                const bool far = gap > 0.f && gap * gap > CGNN_FAR_DP;
                 if (TRAIN) {
                     float cs;
-                    acc += double(trio_train<POL>(me.x, me.y, me.z, tile, lane, cs));
+                    acc += double(far ? trio_train<POL, true>(me.x, me.y, me.z, tile, lane, cs)
+                                      : trio_train<POL, false>(me.x, me.y, me.z, tile, lane, cs));
                     if (32 * J + lane < N) fx_add(&g64[32 * J + lane], double(cs));
                 } else {
-                    acc += 2.0 * double(trio_eval<POL>(me.x, me.y, me.z, tile));
+                    acc += 2.0 * double(far ? trio_eval<POL, true>(me.x, me.y, me.z, tile) : trio_eval<POL, false>(me.x, me.y, me.z, tile));
                 }
             }
         }
@@ -377,7 +389,7 @@ __device__ __forceinline__ void pw_forward(const PwSmem& s, const PairwiseArgs& 
 #pragma unroll
         for (int r = 0; r < 4; ++r)
             if (r0 + r < N) {
-                const int sl = pw_slot_of_row(r0 + r);
+                const int sl = pw_slot_of_row(s.rank[r0 + r]);
                 const float yp = CGNN_PRESCALE * y[r];
                 s.Qd[sl].z = yp; s.Qd[sl + 32].z = yp;
                 s.es[r0 + r] = e[r]; s.yh[r0 + r] = y[r];
@@ -402,7 +414,7 @@ __device__ __forceinline__ void pw_backward_partials(const PwSmem& s, int N, int
             const bool ok = r0 + r < N;
             x[r] = ok ? s.xs[r0 + r] : 0.f;
             e[r] = ok ? s.es[r0 + r] : 0.f;
-            d[r] = ok ? float(fx_get(&s.g64[r0 + r])) * scale : 0.f;
+            d[r] = ok ? float(fx_get(&s.g64[s.rank[r0 + r]])) * scale : 0.f;
         }
         for (int c = 0; c < nchunk; ++c) {
             float v[32];
@@ -456,6 +468,7 @@ __global__ void __launch_bounds__(PW_NT, PW_MIN_CTAS) pairwise_kernel(const Pair
         s.xs = reinterpret_cast<float*>(p);       p += size_t(a.np_max) * 4;
         s.es = reinterpret_cast<float*>(p);       p += size_t(a.np_max) * 4;
         s.yh = reinterpret_cast<float*>(p);       p += size_t(a.np_max) * 4;
+        s.rank = reinterpret_cast<unsigned short*>(p);  p += size_t(a.np_max) * 2;
         s.theta = reinterpret_cast<float*>(p);    p += size_t(Pp) * 4;
         s.am = reinterpret_cast<float*>(p);       p += size_t(Pp) * 4;
         s.av = reinterpret_cast<float*>(p);       p += size_t(Pp) * 4;
@@ -490,17 +503,45 @@ __global__ void __launch_bounds__(PW_NT, PW_MIN_CTAS) pairwise_kernel(const Pair
 
         // ---- load the pair (cause first), prescale, pad, duplicate every tile -------------------
         for (int i = tid; i < NP; i += PW_NT) {
-            float4 t = make_float4(PW_PAD, 0.f, 0.f, 0.f);
+            float x = PW_PAD;
+            if (i < N) { const float2 v = reinterpret_cast<const float2*>(src)[i]; x = dir ? v.y : v.x; }
+            s.xs[i] = (x != x) ? __int_as_float(0x7f800000) : x;      // sort key: NaN rows go last, every rank stays unique
+            const int sl = pw_slot_of_row(i);
+            const float4 pad = make_float4(PW_PAD, 0.f, 0.f, 0.f);
+            s.Qd[sl] = pad; s.Qd[sl + 32] = pad;
+        }
+        __syncthreads();
+        // rank of every row by (x, index): counting sort, N^2 / 512 comparisons per thread, once per instance
+        for (int i = tid; i < NP; i += PW_NT) {
+            int r = i;
+            if (i < N) {
+                const float xi = s.xs[i];
+                r = 0;
+                for (int j = 0; j < N; ++j) {
+                    const float xj = s.xs[j];
+                    r += (xj < xi || (xj == xi && j < i)) ? 1 : 0;
+                }
+            }
+            s.rank[i] = (unsigned short)r;
+        }
+        __syncthreads();
+        for (int i = tid; i < NP; i += PW_NT) {
             float x = 0.f;
             if (i < N) {
                 const float2 v = reinterpret_cast<const float2*>(src)[i];
                 x = dir ? v.y : v.x;
                 const float y = dir ? v.x : v.y;
-                t = make_float4(CGNN_PRESCALE * x, CGNN_PRESCALE * y, 0.f, 0.f);
+                const int sl = pw_slot_of_row(s.rank[i]);
+                const float4 t = make_float4(CGNN_PRESCALE * x, CGNN_PRESCALE * y, 0.f, 0.f);
+                s.Qd[sl] = t; s.Qd[sl + 32] = t;
             }
-            const int sl = pw_slot_of_row(i);
-            s.Qd[sl] = t; s.Qd[sl + 32] = t;
-            s.xs[i] = x; s.es[i] = 0.f; s.yh[i] = 0.f;
+            s.es[i] = 0.f; s.yh[i] = 0.f;
+        }
+        __syncthreads();                                                     // all ranks computed from the keys
+        for (int i = tid; i < NP; i += PW_NT) {                              // keys -> the cause values the generator reads
+            float x = 0.f;
+            if (i < N) { const float2 v = reinterpret_cast<const float2*>(src)[i]; x = dir ? v.y : v.x; }
+            s.xs[i] = x;
         }
         // ---- parameters (GNN.py:21-29, 55-58) and Adam state -------------------------------
         for (int p = tid; p < Pp; p += PW_NT) {
@@ -570,7 +611,7 @@ __global__ void __launch_bounds__(PW_NT, PW_MIN_CTAS) pairwise_kernel(const Pair
             }
             __syncthreads();
             if (a.dbg_dldy)
-                for (int i = tid; i < N; i += PW_NT) a.dbg_dldy[size_t(it) * N + i] = float(fx_get(&s.g64[i])) * gscale;
+                for (int i = tid; i < N; i += PW_NT) a.dbg_dldy[size_t(it) * N + i] = float(fx_get(&s.g64[s.rank[i]])) * gscale;
             pw_backward_partials(s, N, NP, h, tid, warp, lane, gscale);
             __syncthreads();
             for (int p = tid; p < P; p += PW_NT) {

@@ -62,6 +62,38 @@ def test_step_debug_full_size(engine, pol):
         assert relerr(got["params"][s], ref["params"][s]) < TOL
 
 
+@pytest.mark.parametrize("kind", ["binary", "three_levels", "ties_and_outlier", "sorted_descending", "both_directions"])
+def test_cause_column_orderings(engine, kind):
+    """The kernel keeps the rows sorted by the cause column and skips the gamma = 50 kernel for tile pairs whose
+    cause ranges are far apart.  Neither may show: ties (discrete causes), an outlier that stretches the range,
+    already / reversely ordered input, and the swapped direction all have to match the oracle row by row."""
+    n, h = 700, 12
+    rng = np.random.default_rng(77)
+    if kind == "binary":
+        x = rng.integers(0, 2, n).astype(np.float64)
+    elif kind == "three_levels":
+        x = rng.integers(0, 3, n).astype(np.float64)
+    elif kind == "ties_and_outlier":
+        x = np.round(rng.normal(size=n), 1)
+        x[123] = 40.0
+    else:
+        x = np.sort(rng.normal(size=n))[::-1].copy()
+    y = np.tanh(2 * x) + 0.3 * rng.normal(size=n)
+    xy = np.stack([(x - x.mean()) / x.std(), (y - y.mean()) / y.std()], 1).astype(np.float32)
+    if kind == "both_directions":
+        xy = np.ascontiguousarray(xy[:, ::-1])
+    theta0 = (0.05 * rng.normal(size=4 * h + 1)).astype(np.float32)
+    noise = rng.normal(size=(3, n)).astype(np.float32)
+    got = engine.pairwise_step_debug(xy, noise, theta0, h_layer_dim=h)
+    ref = _oracle_train(xy, noise, theta0, h)
+    for s in range(3):
+        assert abs(got["loss"][s] - ref["loss"][s]) <= TOL * abs(ref["loss"][s])
+        assert relerr(got["yhat"][s], ref["yhat"][s]) < TOL
+        assert relerr(got["dldy"][s], ref["dldy"][s]) < TOL
+        assert relerr(got["grad"][s], ref["grad"][s]) < TOL
+        assert relerr(got["params"][s], ref["params"][s]) < TOL
+
+
 @pytest.mark.parametrize("pol", [0, 1, 2, 3])
 def test_trained_state_parity(engine, pol):
     """After 150 Adam steps the loss is ~1e-2 and made of cancelling O(1) block sums: the hard case."""
