@@ -328,11 +328,12 @@ def main():
             "fp32": {"achieved_tflops": ach_flop / 1e12, "peak_tflops": ffma_peak / 1e12, "frac": ach_flop / ffma_peak},
             "kernel_ms_avg": k_ms, "algorithmic_exps_per_launch": exps, "algorithmic_flops_per_launch": flops,
             "traffic_note": "ncu --set full on a 296-instance x 30-step launch of the same kernel: dram read 0.55 MB, "
-                            "write 0 (profiles/r1_pairwise_pol3_trio_ncu_full.txt) - the working set lives in shared memory",
+                            "write 0 (profiles/r1_pairwise_pol3_far_ncu_full.txt) - the working set lives in shared memory",
             "note": "algorithmic count = 7 exp per kernel evaluation (SURVEY 8d); exp_policy p issues 7/5/4/3 MUFU per "
                     "evaluation for p=0/1/2/3 (the others come from exact power relations between the bandwidths), so "
-                    "frac can exceed 1.0; ncu pipe utilisation of this kernel (policy 3, "
-                    "profiles/r1_pairwise_pol3_packed_ncu_full.txt): XU 85 %, issue slots 59 %"}
+                    "frac can exceed 1.0 (policy 3 also drops the gamma=50 exp for tile pairs whose cause "
+                    "ranges are far apart); ncu pipe utilisation of this kernel (profiles/r1_pairwise_pol3_far_ncu_full.txt): "
+                    "XU 76 %, FMA pipe ~77 %, issue slots 63 %"}
 
     out = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
            "warmup": args.warmup, "ms_per_step": dev_ms / args.steps, "higher_is_better": True, "scaling": "weak",
