@@ -299,6 +299,45 @@ __device__ __forceinline__ float warp_reduce32(float (&v)[32], int lane) {
     return v[0];
 }
 
+// The same for N values per lane, N <= 32 (e.g. the 20 hidden units of the default CGNN generator): at every
+// stage the lower lane of a pair keeps the first ceil(n/2) slots, the upper lane the rest (an odd count is padded
+// with a zero), so N = 20 takes 10+5+3+2+1 = 21 shuffles instead of 31.  On return `slot` is the index of the
+// value this lane holds and `valid` tells whether it is a real slot (N < 32 leaves some lanes without one).
+template <int N, int OFS>
+struct WarpReduceN {
+    static __device__ __forceinline__ float run(const float (&v)[N], int lane, int& slot, int& n_valid) {
+        constexpr int H = (N + 1) / 2;
+        const bool up = (lane & OFS) != 0;
+        float w[H];
+#pragma unroll
+        for (int i = 0; i < H; ++i) {
+            const float hi = (H + i < N) ? v[(H + i < N) ? H + i : 0] : 0.f;
+            const float send = up ? v[i] : hi;
+            const float keep = up ? hi : v[i];
+            w[i] = keep + __shfl_xor_sync(0xffffffffu, send, OFS);
+        }
+        slot += up ? H : 0;
+        n_valid = up ? max(n_valid - H, 0) : min(n_valid, H);
+        return WarpReduceN<H, OFS / 2>::run(w, lane, slot, n_valid);
+    }
+};
+template <int N>
+struct WarpReduceN<N, 0> {
+    static __device__ __forceinline__ float run(const float (&v)[N], int, int&, int&) {
+        static_assert(N == 1, "32 lanes reduce at most 32 slots");
+        return v[0];
+    }
+};
+template <int N>
+__device__ __forceinline__ float warp_reduce_n(const float (&v)[N], int lane, int& slot, bool& valid) {
+    static_assert(N >= 1 && N <= 32, "1..32 slots");
+    slot = 0;
+    int n_valid = N;
+    const float r = WarpReduceN<N, 16>::run(v, lane, slot, n_valid);
+    valid = n_valid >= 1;
+    return r;
+}
+
 // ---------------------------------------------------------------------------------------------
 // TF-1 Adam, fp32, one parameter per call.  lr_t = lr*sqrt(1-b2^t)/(1-b1^t) is computed by the caller.
 // ---------------------------------------------------------------------------------------------

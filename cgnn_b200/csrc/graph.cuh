@@ -384,7 +384,6 @@ __device__ __forceinline__ void gr_backward_block(const GrSmem& s, const float* 
     const GraphDesc& g = *s.desc;
     for (int k = g.n_var - 1; k >= 0; --k) {
         float2 z[HP / 2];
-        float v[32];
         gr_node_z<DP, HP>(s, nb, k, i, lane, z);
         const int n_in = g.n_in[k], n_par = g.n_par[k];
         const int off = g.pad_off[k];
@@ -394,13 +393,15 @@ __device__ __forceinline__ void gr_backward_block(const GrSmem& s, const float* 
         // b_out
         const float sb = warp_sum(delta);
         if (lane == 0) fx_add(&s.g64[off + (n_in + 2) * HP], double(sb));
-        // W_out, then dz in place of z
+        // W_out, then dz in place of z.  Sums over the 32 rows: transposing reduction over the HP hidden units;
+        // lane -> (slot, valid) is the same for every reduction of this width
+        float v[HP];
+        int slot;
+        bool has_slot;
 #pragma unroll
-        for (int kk = 0; kk < 32; ++kk) {
-            v[kk] = (kk < HP) ? fmaxf(gr_zget<HP>(z, kk), 0.f) * delta : 0.f;
-        }
-        float r = warp_reduce32(v, lane);
-        if (lane < HP) fx_add(&s.g64[off + (n_in + 1) * HP + lane], double(r));
+        for (int kk = 0; kk < HP; ++kk) v[kk] = fmaxf(gr_zget<HP>(z, kk), 0.f) * delta;
+        float r = warp_reduce_n<HP>(v, lane, slot, has_slot);
+        if (has_slot) fx_add(&s.g64[off + (n_in + 1) * HP + slot], double(r));
 #pragma unroll
         for (int q = 0; q < HP / 2; ++q) {
             z[q].x = z[q].x > 0.f ? delta * w_out[2 * q] : 0.f;
@@ -408,18 +409,16 @@ __device__ __forceinline__ void gr_backward_block(const GrSmem& s, const float* 
         }
         // b_in
 #pragma unroll
-        for (int kk = 0; kk < 32; ++kk)
-            v[kk] = (kk < HP) ? (gr_zget<HP>(z, kk)) : 0.f;
-        r = warp_reduce32(v, lane);
-        if (lane < HP) fx_add(&s.g64[off + n_in * HP + lane], double(r));
+        for (int kk = 0; kk < HP; ++kk) v[kk] = gr_zget<HP>(z, kk);
+        r = warp_reduce_n<HP>(v, lane, slot, has_slot);
+        if (has_slot) fx_add(&s.g64[off + n_in * HP + slot], double(r));
         // W_in rows and input gradients
         for (int p = 0; p < n_in; ++p) {
             const float u = (p < n_par) ? s.Pm[i * DP + idx[p]] : nb[idx[p] * 32 + lane];
 #pragma unroll
-            for (int kk = 0; kk < 32; ++kk)
-                v[kk] = (kk < HP) ? u * (gr_zget<HP>(z, kk)) : 0.f;
-            r = warp_reduce32(v, lane);
-            if (lane < HP) fx_add(&s.g64[off + p * HP + lane], double(r));
+            for (int kk = 0; kk < HP; ++kk) v[kk] = u * gr_zget<HP>(z, kk);
+            r = warp_reduce_n<HP>(v, lane, slot, has_slot);
+            if (has_slot) fx_add(&s.g64[off + p * HP + slot], double(r));
             if (p < n_par) {
                 const float4* w4 = reinterpret_cast<const float4*>(s.theta + off + p * HP);
                 float2 du = make_float2(0.f, 0.f);
