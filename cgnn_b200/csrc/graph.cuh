@@ -10,9 +10,11 @@
 //
 // Layout: the generated matrix Pm[NP][DP] (row-major, DP = n_var padded to a multiple of 4, pad
 // columns 0) lives in shared memory for the instance's whole life; the observed matrix T[NP][DP]
-// is the same for every instance of a batch (or one per row subset) and is streamed through the
-// read-only path (L1/L2 resident: <= 192 KB).  Parameters, Adam moments and the fixed-point
-// gradient accumulators are in shared memory too.
+// is the same for every instance of a batch (or one per row subset).  It is copied to shared memory next
+// to Pm when both fit one SM (t_smem); otherwise every warp streams it through a cp.async ring that lives
+// in its (idle) noise buffer, two halves of 16 rows (t_ring); only when neither is possible (random-feature
+// mode, very narrow noise buffers) is it read through the read-only path (L1/L2).  Parameters, Adam moments
+// and the fixed-point gradient accumulators are in shared memory too.
 //
 // Mapping: lane <-> row i.  A warp owns whole 32-row blocks (w, w+NW, ...): the row's generated
 // values, its MMD gradient accumulators and the distance differences stay in REGISTERS across all
