@@ -32,6 +32,17 @@ def test_hparams_struct_layout_matches_header():
     assert ctypes.sizeof(_lib.GraphBatchStruct) == 16 + 5 * 8
 
 
+def test_header_constants_match_the_host_layer():
+    """Limits and the automatic exp policy: the numbers in the header are the numbers the Python layer uses."""
+    text = open(os.path.join(ROOT, "include", "cgnn_b200.h")).read()
+    defs = {k: int(v) for k, v in re.findall(r"#define\s+(CGNN_\w+)\s+\(?(-?\d+)\)?\s", text)}
+    from cgnn_b200 import SETTINGS
+    assert defs["CGNN_EXP_POLICY_AUTO"] == -1 and SETTINGS.exp_policy == defs["CGNN_EXP_POLICY_AUTO"]
+    assert defs["CGNN_EXP_POLICY_PAIRWISE"] == 3 and defs["CGNN_EXP_POLICY_GRAPH"] == 1
+    assert defs["CGNN_MAX_ROWS_PAIRWISE"] >= SETTINGS.max_nb_points and defs["CGNN_MAX_ROWS_GRAPH"] >= SETTINGS.max_nb_points
+    assert defs["CGNN_MAX_FAST_VECTORS"] >= SETTINGS.nb_vectors_approx_MMD
+
+
 def test_no_gpu_means_loud_failure():
     """Without an sm_100 device the product raises; it never falls back to the oracle or the CPU."""
     import torch
