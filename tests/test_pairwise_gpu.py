@@ -94,6 +94,27 @@ def test_cause_column_orderings(engine, kind):
         assert relerr(got["params"][s], ref["params"][s]) < TOL
 
 
+@pytest.mark.parametrize("pol", [0, 3])
+@pytest.mark.parametrize("n", [33, 40, 64, 65, 97, 130, 2047, 2048])
+def test_far_tile_pairs_at_awkward_sizes(engine, n, pol):
+    """Two well separated clusters of causes make far tile pairs even in tiny instances: partially filled last
+    tiles, odd and even tile counts, one row in the last tile, the maximum row count."""
+    h = 6
+    rng = np.random.default_rng(1000 + n)
+    x = np.where(rng.random(n) < 0.45, rng.normal(-2.0, 0.2, n), rng.normal(2.0, 0.3, n))
+    y = np.sin(x) + 0.5 * rng.normal(size=n)
+    xy = np.stack([(x - x.mean()) / x.std(), (y - y.mean()) / y.std()], 1).astype(np.float32)
+    theta0 = (0.3 * rng.normal(size=4 * h + 1)).astype(np.float32)
+    steps = 1 if n > 2000 else 2
+    noise = rng.normal(size=(steps, n)).astype(np.float32)
+    got = engine.pairwise_step_debug(xy, noise, theta0, h_layer_dim=h, exp_policy=pol)
+    ref = _oracle_train(xy, noise, theta0, h)
+    for s in range(steps):
+        assert abs(got["loss"][s] - ref["loss"][s]) <= TOL * abs(ref["loss"][s])
+        assert relerr(got["dldy"][s], ref["dldy"][s]) < TOL
+        assert relerr(got["grad"][s], ref["grad"][s]) < TOL
+
+
 @pytest.mark.parametrize("pol", [0, 1, 2, 3])
 def test_trained_state_parity(engine, pol):
     """After 150 Adam steps the loss is ~1e-2 and made of cancelling O(1) block sums: the hard case."""
