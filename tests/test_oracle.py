@@ -68,3 +68,22 @@ def test_graph_plan_and_forward_shapes():
         rng = np.random.default_rng(0)
         r = oc.step_debug(0.05 * rng.normal(size=P), make_data(40, 9, 1), rng.normal(size=(op["n_noise"], 40)), op, 6)
         assert r["pred"].shape == (40, 9) and r["grad"].shape == (P,) and np.isfinite(r["loss"])
+
+
+def test_far_tile_threshold_bound():
+    """The pairwise kernel leaves the gamma = 50 kernel out for tile pairs whose cause ranges are more than
+    CGNN_FAR_DP (primed units, D' = 0.25 log2(e) D) apart.  The dropped term against the smallest retained one,
+    and against the whole weight sum of Loss.py:10's bandwidth list, at the threshold (it only shrinks beyond)."""
+    import math
+    import re
+    import os
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    txt = open(os.path.join(root, "cgnn_b200", "csrc", "common.cuh")).read()
+    far_dp = float(re.search(r"#define\s+CGNN_FAR_DP\s+([0-9.]+)f", txt).group(1))
+    d = far_dp / (0.25 * math.log2(math.e))
+    gam = [0.005, 0.05, 0.25, 0.5, 1.0, 5.0, 50.0]
+    dropped_w, dropped_k = 50.0 * math.exp(-50.0 * d), math.exp(-50.0 * d)
+    kept_w = sum(g * math.exp(-g * d) for g in gam[:-1])
+    kept_k = sum(math.exp(-g * d) for g in gam[:-1])
+    assert dropped_w / (0.005 * math.exp(-0.005 * d)) < 1e-8          # against the widest kernel alone
+    assert dropped_w / kept_w < 1e-10 and dropped_k / kept_k < 1e-12   # against what is actually summed
