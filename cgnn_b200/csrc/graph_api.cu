@@ -234,14 +234,21 @@ static int run_graph_impl(cgnn_ctx* ctx, const cgnn_hparams* hp, const float* da
     for (int csz = min_csz; csz <= 4; ++csz) {
         if (dbg_host && csz > 1) break;                              // the parity probe runs on one CTA
         if (hp->graph_cluster > 0 && csz != hp->graph_cluster) continue;
+        if (hp->graph_cluster == 0 && csz > min_csz && (NB + csz - 1) / csz < 4) continue;   // fixed costs dominate tiny shares
         int slots = 0;
         if (launch_graph(DP, HP, pol, a, -1, csz, smem, ctx->stream, &slots) != cudaSuccess || slots < 1) {
             cudaGetLastError();
             continue;
         }
+        // Time of one instance on a cluster of csz CTAs, in units of "one round of 16 row blocks on a full SM":
+        // a warp owns a row block, a CTA works through ceil(rb/16) rounds, and a round with w < 16 busy warps is
+        // shorter because the warps share the SM's pipes - measured on B200 (tools/bench_graph_cluster.py):
+        // w = 16/12/8/6/4 -> 1.00/0.875/0.70/0.69/0.55, i.e. about 0.4 + 0.6 w/16; a cluster adds ~6 % (two
+        // cluster barriers per step, replicated generator forward).
         const int rb_per_cta = (NB + csz - 1) / csz;
-        const double rounds_rows = double((rb_per_cta + GR_NW - 1) / GR_NW);          // row-block rounds per step
-        const double cost = std::ceil(double(n_inst) / slots) * (rounds_rows + 0.1);  // 0.1: replicated forward, cluster syncs
+        const int tail_w = rb_per_cta % GR_NW;
+        const double t_inst = double(rb_per_cta / GR_NW) + (tail_w ? 0.4 + 0.6 * tail_w / GR_NW : 0.0) + (csz > 1 ? 0.06 : 0.0);
+        const double cost = std::ceil(double(n_inst) / slots) * t_inst;
         if (cost < best_cost * 0.999) { best_cost = cost; best_csz = csz; best_slots = slots; }
     }
     if (best_cost >= 1e300) return fail(ctx, CGNN_ERR_CUDA, "graph kernel cannot be launched (cluster size %d, %zu B smem)", hp->graph_cluster, smem);
