@@ -225,12 +225,11 @@ static int run_graph_impl(cgnn_ctx* ctx, const cgnn_hparams* hp, const float* da
     const int pol = hp->exp_policy < 0 ? CGNN_EXP_POLICY_GRAPH : hp->exp_policy;
     // ---- CTAs per instance: a cluster when the batch cannot fill the GPU with one CTA per instance ----------
     const int NB = NP / 32;
-    int best_csz = 1, best_slots = std::max(1, ctx->prop.multiProcessorCount);
-    double best_cost = 1e300;
     const int min_csz = a.fast_k > 0 ? (NB + GR_NW - 1) / GR_NW : 1;   // random-feature mode: one row block per warp
     if (min_csz > 4 || (dbg_host && min_csz > 1))
         return fail(ctx, CGNN_ERR_LIMIT, "random-feature loss on the graph path: n_rows=%d needs a cluster of %d CTAs (limit %d)",
                     n_rows, min_csz, dbg_host ? 1 : 4);
+    int slots_of[5] = {0, 0, 0, 0, 0};                                  // resident clusters per cluster size
     for (int csz = min_csz; csz <= 4; ++csz) {
         if (dbg_host && csz > 1) break;                              // the parity probe runs on one CTA
         if (hp->graph_cluster > 0 && csz != hp->graph_cluster) continue;
@@ -240,26 +239,53 @@ static int run_graph_impl(cgnn_ctx* ctx, const cgnn_hparams* hp, const float* da
             cudaGetLastError();
             continue;
         }
-        // Time of one instance on a cluster of csz CTAs, in units of "one round of 16 row blocks on a full SM":
-        // a warp owns a row block, a CTA works through ceil(rb/16) rounds, and a round with w < 16 busy warps is
-        // shorter because the warps share the SM's pipes - measured on B200 (tools/bench_graph_cluster.py):
-        // w = 16/12/8/6/4 -> 1.00/0.875/0.70/0.69/0.55, i.e. about 0.4 + 0.6 w/16; a cluster adds ~6 % (two
-        // cluster barriers per step, replicated generator forward).
-        const int rb_per_cta = (NB + csz - 1) / csz;
-        const int tail_w = rb_per_cta % GR_NW;
-        const double t_inst = double(rb_per_cta / GR_NW) + (tail_w ? 0.4 + 0.6 * tail_w / GR_NW : 0.0) + (csz > 1 ? 0.06 : 0.0);
-        const double cost = std::ceil(double(n_inst) / slots) * t_inst;
-        if (cost < best_cost * 0.999) { best_cost = cost; best_csz = csz; best_slots = slots; }
+        slots_of[csz] = slots;
     }
-    if (best_cost >= 1e300) return fail(ctx, CGNN_ERR_CUDA, "graph kernel cannot be launched (cluster size %d, %zu B smem)", hp->graph_cluster, smem);
-    const int n_clusters = std::min(n_inst, best_slots);
-    ctx->last_cluster = best_csz;
+    // Time of one instance on a cluster of csz CTAs, in units of "one round of 16 row blocks on a full SM":
+    // a warp owns a row block, a CTA works through ceil(rb/16) rounds, and a round with w < 16 busy warps is
+    // shorter because the warps share the SM's pipes - measured on B200 (tools/bench_graph_cluster.py):
+    // w = 16/12/8/6/4 -> 1.00/0.875/0.70/0.69/0.55, i.e. about 0.4 + 0.6 w/16; a cluster adds ~6 % (two
+    // cluster barriers per step, replicated generator forward).
+    struct Choice { int csz, slots; double t_inst, cost; };
+    auto choose = [&](int n) {
+        Choice best{0, 0, 0.0, 1e300};
+        for (int csz = 1; csz <= 4; ++csz) {
+            if (slots_of[csz] < 1) continue;
+            const int rb_per_cta = (NB + csz - 1) / csz;
+            const int tail_w = rb_per_cta % GR_NW;
+            const double t_inst = double(rb_per_cta / GR_NW) + (tail_w ? 0.4 + 0.6 * tail_w / GR_NW : 0.0) + (csz > 1 ? 0.06 : 0.0);
+            const double cost = std::ceil(double(n) / slots_of[csz]) * t_inst;
+            if (cost < best.cost * 0.999) best = Choice{csz, slots_of[csz], t_inst, cost};
+        }
+        return best;
+    };
+    const Choice mainc = choose(n_inst);
+    if (mainc.csz == 0) return fail(ctx, CGNN_ERR_CUDA, "graph kernel cannot be launched (cluster size %d, %zu B smem)", hp->graph_cluster, smem);
+    ctx->last_cluster = mainc.csz;
+    // A batch just above a multiple of the resident count pays a whole wave for its remainder.  The remainder is
+    // launched on its own, with the cluster size that suits IT (results do not depend on the cluster size).
+    const int full = (n_inst / mainc.slots) * mainc.slots, rem = n_inst - full;
+    Choice tailc{0, 0, 0.0, 1e300};
+    if (hp->graph_cluster == 0 && !dbg_host && full > 0 && rem > 0) {
+        tailc = choose(rem);
+        if (!(tailc.csz != mainc.csz && tailc.cost < 0.93 * mainc.t_inst)) tailc.csz = 0;
+    }
 
     CU(cudaEventRecord(ctx->ev0, ctx->stream));
-    cudaError_t le = launch_graph(DP, HP, pol, a, n_clusters, best_csz, smem, ctx->stream, nullptr);
+    cudaError_t le;
+    if (tailc.csz) {
+        GraphArgs a1 = a, a2 = a;
+        a1.n_inst = full;
+        a2.n_inst = rem; a2.inst = a.inst + full; a2.inst_uid = a.inst_uid + full; a2.counter = a.counter + 32;
+        le = launch_graph(DP, HP, pol, a1, std::min(full, mainc.slots), mainc.csz, smem, ctx->stream, nullptr);
+        if (le == cudaSuccess) le = launch_graph(DP, HP, pol, a2, std::min(rem, tailc.slots), tailc.csz, smem, ctx->stream, nullptr);
+        ctx->last_launches = 3;
+    } else {
+        le = launch_graph(DP, HP, pol, a, std::min(n_inst, mainc.slots), mainc.csz, smem, ctx->stream, nullptr);
+        ctx->last_launches = 2;
+    }
     if (le != cudaSuccess) return fail(ctx, CGNN_ERR_CUDA, "graph kernel launch: %s", cudaGetErrorString(le));
     CU(cudaEventRecord(ctx->ev1, ctx->stream));
-    ctx->last_launches = 2;
 
     if ((rc = copy_back(ctx, scores, a.scores, sizeof(float) * n_inst))) return rc;
     if ((rc = copy_back(ctx, loss_trace, a.trace, sizeof(float) * size_t(n_inst) * epochs))) return rc;
