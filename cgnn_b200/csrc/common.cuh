@@ -210,7 +210,10 @@ __device__ __forceinline__ float2 ex2f2(float2 x) { return make_float2(ex2f(x.x)
 // FAR: the caller guarantees Dp > CGNN_FAR_DP for both halves; the gamma = 50 kernel is then below 5e-11 and left out.
 #define CGNN_FAR_DP 0.2f          /* primed units: D > 0.5545; 50 e^{-50 D} / (0.005 e^{-0.005 D}) < 1e-8 */
 
-template <int POL, bool FAR = false>
+// FAR = 2 ("very far", Dp > CGNN_FAR2_DP): the gamma = 5 kernel is out of sight as well.
+#define CGNN_FAR2_DP 1.85f        /* D > 5.13; 5 e^{-5 D} / (0.005 e^{-0.005 D}) < 1e-8 */
+
+template <int POL, int FAR = 0>
 __device__ __forceinline__ float2 wsum_p2(float2 Dp) {
     const float2 q = ex2f2(fmul2(Dp, splat2(-0.02f)));
     const float2 p = ex2f2(make_float2(-Dp.x, -Dp.y));
@@ -224,7 +227,8 @@ __device__ __forceinline__ float2 wsum_p2(float2 Dp) {
     if (POL >= 1) {
         const float2 p2 = fmul2(p, p);
         w = ffma2(ffma2(fadd2(p2, splat2(G3)), p, splat2(G2)), p, w);
-        if (POL >= 3) { const float2 p4 = fmul2(p2, p2), p8 = fmul2(p4, p4); w = ffma2(splat2(G5), fmul2(fmul2(p8, p8), p4), w); }
+        if (FAR >= 2) { }
+        else if (POL >= 3) { const float2 p4 = fmul2(p2, p2), p8 = fmul2(p4, p4); w = ffma2(splat2(G5), fmul2(fmul2(p8, p8), p4), w); }
         else w = ffma2(splat2(G5), ex2f2(fmul2(Dp, splat2(-20.0f))), w);
     } else {
         w = ffma2(splat2(G2), p, w);
@@ -235,7 +239,7 @@ __device__ __forceinline__ float2 wsum_p2(float2 Dp) {
     return w;
 }
 
-template <int POL, bool FAR = false>
+template <int POL, int FAR = 0>
 __device__ __forceinline__ float2 ksum_p2(float2 Dp) {
     const float2 q = ex2f2(fmul2(Dp, splat2(-0.02f)));
     const float2 p = ex2f2(make_float2(-Dp.x, -Dp.y));
@@ -245,7 +249,8 @@ __device__ __forceinline__ float2 ksum_p2(float2 Dp) {
     if (POL >= 1) {
         const float2 p2 = fmul2(p, p), p4 = fmul2(p2, p2);
         float2 t = fadd2(ffma2(p2, p2, p2), p);
-        if (POL >= 3) { const float2 p8 = fmul2(p4, p4); t = ffma2(fmul2(p8, p8), p4, t); }
+        if (FAR >= 2) { }
+        else if (POL >= 3) { const float2 p8 = fmul2(p4, p4); t = ffma2(fmul2(p8, p8), p4, t); }
         else t = fadd2(t, ex2f2(fmul2(Dp, splat2(-20.0f))));
         s = fadd2(s, t);
     } else {

@@ -115,7 +115,7 @@ __device__ __forceinline__ int pw_npp(int I, int NB) {
 // Off-diagonal tile pair, gradient form.  tile = &Qd[64 J + lane].  Returns the row-side sum for row i;
 // colsum receives the total for column 32 J + lane (both in primed units, unscaled).  Two steps of the
 // walk are evaluated together: their six kernel evaluations run as three FP32x2-packed chains.
-template <int POL, bool FAR>
+template <int POL, int FAR>
 __device__ __forceinline__ float trio_train(float xi, float yi, float yhi, const float4* __restrict__ tile, int lane,
                                             float& colsum) {
     float2 ra = make_float2(0.f, 0.f);
@@ -159,7 +159,7 @@ __device__ __forceinline__ float duo_train(float xi, float yhi, const float4* __
 }
 
 // Loss forms: kPP - kPT(i,j) - kPT(j,i) per unordered pair (to be doubled), kPP - 2 kPT per ordered pair.
-template <int POL, bool FAR>
+template <int POL, int FAR>
 __device__ __forceinline__ float trio_eval(float xi, float yi, float yhi, const float4* __restrict__ tile) {
     float2 acc = make_float2(0.f, 0.f);
     CGNN_UNROLL(CGNN_TRIO_UNROLL)
@@ -221,14 +221,17 @@ __device__ double mmd_pass(const float4* __restrict__ Qd, long long* g64, int N,
                 const float4* tile = Qd + 64 * J + lane;
                 // rows are sorted by x: the gap between the x ranges of the two tiles bounds every (x_i - x_j)^2
                 const float gap = (J > I) ? Qd[64 * J].x - Qd[64 * I + 31].x : Qd[64 * I].x - Qd[64 * J + 31].x;
-                const bool far = gap > 0.f && gap * gap > CGNN_FAR_DP;
+                const float g2 = gap > 0.f ? gap * gap : 0.f;
+                const int far = g2 > CGNN_FAR2_DP ? 2 : g2 > CGNN_FAR_DP ? 1 : 0;
                 if (TRAIN) {
                     float cs;
-                    acc += double(far ? trio_train<POL, true>(me.x, me.y, me.z, tile, lane, cs)
-                                      : trio_train<POL, false>(me.x, me.y, me.z, tile, lane, cs));
+                    acc += double(far == 2 ? trio_train<POL, 2>(me.x, me.y, me.z, tile, lane, cs)
+                                  : far == 1 ? trio_train<POL, 1>(me.x, me.y, me.z, tile, lane, cs)
+                                             : trio_train<POL, 0>(me.x, me.y, me.z, tile, lane, cs));
                     if (32 * J + lane < N) fx_add(&g64[32 * J + lane], double(cs));
                 } else {
-                    acc += 2.0 * double(far ? trio_eval<POL, true>(me.x, me.y, me.z, tile) : trio_eval<POL, false>(me.x, me.y, me.z, tile));
+                    acc += 2.0 * double(far == 2 ? trio_eval<POL, 2>(me.x, me.y, me.z, tile)
+                                        : far == 1 ? trio_eval<POL, 1>(me.x, me.y, me.z, tile) : trio_eval<POL, 0>(me.x, me.y, me.z, tile));
                 }
             }
         }

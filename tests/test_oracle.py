@@ -87,3 +87,8 @@ def test_far_tile_threshold_bound():
     kept_k = sum(math.exp(-g * d) for g in gam[:-1])
     assert dropped_w / (0.005 * math.exp(-0.005 * d)) < 1e-8          # against the widest kernel alone
     assert dropped_w / kept_w < 1e-10 and dropped_k / kept_k < 1e-12   # against what is actually summed
+    # second level ("very far"): the gamma = 5 kernel goes as well
+    far2_dp = float(re.search(r"#define\s+CGNN_FAR2_DP\s+([0-9.]+)f", txt).group(1))
+    d2 = far2_dp / (0.25 * math.log2(math.e))
+    assert (5.0 * math.exp(-5.0 * d2) + 50.0 * math.exp(-50.0 * d2)) / (0.005 * math.exp(-0.005 * d2)) < 1e-8
+    assert (math.exp(-5.0 * d2) + math.exp(-50.0 * d2)) / sum(math.exp(-g * d2) for g in gam[:-2]) < 1e-10
