@@ -174,6 +174,44 @@ def golden_graph(tf, ref, conf):
                         list_nodes=np.array(plan["list_nodes"]))
 
 
+def golden_graph_fourier(tf, ref):
+    """CGNN_tf with use_Fast_MMD=True (CGNN.py:92-93 -> Loss.py:35-56): the graph generator trained against the
+    random-feature loss; the fixture keeps every matrix the reference's rp() drew."""
+    from oracle import GAMMAS
+    from oracle import cgnn as oc
+    g = _small_graph(ref, False)
+    plan = oc.build_plan(g)
+    n, h, tr, te, nv = 64, 5, 7, 3, 4
+    raw = pd.read_csv(os.path.join(ROOT, "examples", "Example_graph_numdata.csv"))[plan["list_nodes"]].values[:n]
+    data = ((raw - raw.mean(0)) / raw.std(0)).astype("float32")
+    tf.reset(seed=33)
+    model = ref["CGNN"].CGNN_tf(n, g, 0, 0, h_layer_dim=h, learning_rate=0.01, init_std=0.05, use_Fast_MMD=True,
+                                nb_vectors_approx_MMD=nv)
+    _quiet(model.train, data, verbose=False, train_epochs=tr)
+    score = _quiet(model.evaluate, data, verbose=False, test_epochs=te)
+    n_var = plan["n_var"]
+    init, runs = _split_draws(tf, 4 * n_var)
+    theta0 = np.concatenate([np.concatenate([t.reshape(-1) for t in init[4 * k:4 * k + 4]]) for k in range(n_var)])
+    ids = sorted(set(d[0] for d in runs))          # creation order: the nodes' noise (build order), then rp(): 7 normal blocks, phases
+    assert len(ids) == n_var + 8
+    per = {i: [d[2] for d in runs if d[0] == i] for i in ids}
+    steps = tr + te
+    noise = np.zeros((steps, plan["n_noise"], n))
+    for pos in range(n_var):
+        for s in range(steps):
+            noise[s, plan["nodes"][pos]["col"]] = per[ids[pos]][s][:, 0]
+    wz = np.stack([np.concatenate([np.concatenate([2.0 * gam * per[ids[n_var + j]][s] for j, gam in enumerate(GAMMAS)], 0),
+                                   per[ids[n_var + 7]][s]], 1).T for s in range(steps)])
+    assert wz.shape == (steps, n_var + 1, 7 * nv)
+    losses = np.array([r[0] for r in tf.RUN_LOG if len(r)], dtype=np.float64)
+    assert losses.shape == (steps,)
+    np.savez_compressed(os.path.join(OUT, "ref_shim_graph_fourier.npz"), data=data, h=h, train=tr, test=te, k=nv, theta0=theta0,
+                        noise=noise, wz=wz, losses=losses, score=score,
+                        edges=np.array(g.get_list_edges(order_by_weight=False, return_weights=False)),
+                        weights=np.array([w for _, _, w in g.get_list_edges(order_by_weight=False)]),
+                        skeleton=np.array([]), list_nodes=np.array(plan["list_nodes"]))
+
+
 def main():
     import refload
     from oracle import tf1_shim as tf
@@ -185,6 +223,7 @@ def main():
     golden_pairwise(tf, ref)
     golden_graph(tf, ref, False)
     golden_graph(tf, ref, True)
+    golden_graph_fourier(tf, ref)
     for f in sorted(os.listdir(OUT)):
         print(f, os.path.getsize(os.path.join(OUT, f)))
 

@@ -47,6 +47,20 @@ def test_graph_fixtures(engine, name, conf, pol):
     assert abs(r["scores"][0, 0] - float(z["score"])) < 2 * TOL * float(z["score"])
 
 
+def test_graph_fourier_fixture(engine):
+    """The graph kernel in random-feature mode against the reference's CGNN_tf(use_Fast_MMD=True): the training
+    losses with the rp() matrices the reference drew (2e-4: the fp32 floor of this loss, tests/test_pairwise_gpu.py)."""
+    import cgnn_b200.utils.Graph as my_graph
+    from cgnn_b200.plan import build_plan
+    z = np.load(os.path.join(GOLD, "ref_shim_graph_fourier.npz"))
+    plan = build_plan(graph_from_fixture(z, my_graph))
+    h, tr, k = int(z["h"]), int(z["train"]), int(z["k"])
+    got = engine.graph_step_debug(z["data"], plan, z["noise"][:tr].astype(np.float32), z["theta0"].astype(np.float32),
+                                  fourier_wz=z["wz"][:tr].astype(np.float32), h_layer_dim=h, use_Fast_MMD=True,
+                                  nb_vectors_approx_MMD=k)
+    assert relerr(got["loss"], z["losses"][:tr]) < 2e-4
+
+
 def test_mmd_fixture_through_the_graph_kernel(engine):
     """Loss.MMD_loss_tf on raw matrices: a graph with no edges and zero input weights generates
     pred = b_out per column, so instead the fixture is checked by making `pred` the generator's

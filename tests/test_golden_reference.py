@@ -89,6 +89,29 @@ def test_fourier_loss_and_fast_mmd_generator():
     assert abs(score - float(z["f_score"])) < TIGHT * score
 
 
+def test_graph_generator_with_the_random_feature_loss():
+    """CGNN_tf(use_Fast_MMD=True) of the reference (CGNN.py:92-93): losses of every train and evaluate sess.run
+    and the evaluate() mean, replayed by the oracle with the recorded noise and rp() matrices."""
+    import cgnn_b200.utils.Graph as my_graph
+    from oracle import cgnn as oc
+    from oracle.adam import TFAdam
+    z = np.load(os.path.join(GOLD, "ref_shim_graph_fourier.npz"))
+    g = graph_from_fixture(z, my_graph)
+    plan = oc.build_plan(g)
+    assert plan["list_nodes"] == z["list_nodes"].tolist()
+    data, h, tr, te, k = z["data"].astype(np.float64), int(z["h"]), int(z["train"]), int(z["test"]), int(z["k"])
+    theta = z["theta0"].astype(np.float64)
+    opt = TFAdam(theta.size, 0.01)
+    losses = []
+    for s in range(tr + te):
+        r = oc.step_debug(theta, data, z["noise"][s], plan, h, wz=z["wz"][s], k=k)
+        losses.append(r["loss"])
+        if s < tr:
+            theta = opt.step(theta, r["grad"])
+    np.testing.assert_allclose(losses, z["losses"], rtol=TIGHT)
+    assert abs(np.mean(losses[tr:]) - float(z["score"])) < TIGHT * float(z["score"])
+
+
 def test_rp_literal_shape_and_scales():
     from oracle.mmd import rp_literal
     from oracle import GAMMAS
