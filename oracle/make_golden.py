@@ -212,6 +212,48 @@ def golden_graph_fourier(tf, ref):
                         skeleton=np.array([]), list_nodes=np.array(plan["list_nodes"]))
 
 
+def golden_run_instance(tf, ref):
+    """run_CGNN_tf / run_CGNN_confounders_tf (CGNN.py:163-195, CGNN_confounders.py:182-216): the per-instance entry
+    the search drivers call, fed with a DataFrame whose columns are NOT in the graph's node order - the reference
+    re-orders them itself (`df_data[list_nodes]`).  Noise and initial parameters are stored per build position,
+    not in any engine layout, so the replaying side has to do its own column mapping."""
+    from oracle import cgnn as oc
+    out = {}
+    for conf in (False, True):
+        g = _small_graph(ref, conf)
+        plan = oc.build_plan(g, confounders=conf)
+        n, h, tr, te = 48, 4, 6, 3
+        raw = pd.read_csv(os.path.join(ROOT, "examples", "Example_graph_numdata.csv"))[plan["list_nodes"]].values[:n]
+        std = ((raw - raw.mean(0)) / raw.std(0)).astype("float32")
+        cols = list(plan["list_nodes"])
+        shuffled = [cols[k] for k in np.random.default_rng(5 + conf).permutation(len(cols))]
+        df = pd.DataFrame(std, columns=cols)[shuffled]
+        tf.reset(seed=51 + conf)
+        ref["Settings"].SETTINGS.GPU = True
+        fn = ref["CGNN_confounders"].run_CGNN_confounders_tf if conf else ref["CGNN"].run_CGNN_tf
+        score = _quiet(fn, df, g, 0, 0, gpu=True, nb_gpu=1, gpu_offset=0, h_layer_dim=h, train_epochs=tr, test_epochs=te,
+                       verbose=False)
+        n_var = plan["n_var"]
+        init, runs = _split_draws(tf, 4 * n_var)
+        theta0 = np.concatenate([np.concatenate([t.reshape(-1) for t in init[4 * k:4 * k + 4]]) for k in range(n_var)])
+        ids = sorted(set(d[0] for d in runs))      # creation order: shared (one per skeleton edge), then own noise in build order
+        per = {i: [d[2][:, 0] for d in runs if d[0] == i] for i in ids}
+        n_shared = plan["n_noise"] - n_var
+        steps = tr + te
+        shared = np.stack([[per[ids[e]][s] for e in range(n_shared)] for s in range(steps)]) if n_shared else np.zeros((steps, 0, n))
+        own = np.stack([[per[ids[n_shared + pos]][s] for pos in range(n_var)] for s in range(steps)])
+        losses = np.array([r[0] for r in tf.RUN_LOG if len(r)], dtype=np.float64)
+        assert losses.shape == (steps,)
+        tag = "conf_" if conf else "plain_"
+        out.update({tag + "data": df.values, tag + "columns": np.array(shuffled), tag + "h": h, tag + "train": tr, tag + "test": te,
+                    tag + "theta0": theta0, tag + "own_noise": own, tag + "shared_noise": shared, tag + "losses": losses,
+                    tag + "score": score,
+                    tag + "edges": np.array(g.get_list_edges(order_by_weight=False, return_weights=False)),
+                    tag + "weights": np.array([w for _, _, w in g.get_list_edges(order_by_weight=False)]),
+                    tag + "skeleton": np.array(g.skeleton.get_list_edges_without_duplicate() if conf else [])})
+    np.savez_compressed(os.path.join(OUT, "ref_shim_run_instance.npz"), **out)
+
+
 def main():
     import refload
     from oracle import tf1_shim as tf
@@ -224,6 +266,7 @@ def main():
     golden_graph(tf, ref, False)
     golden_graph(tf, ref, True)
     golden_graph_fourier(tf, ref)
+    golden_run_instance(tf, ref)
     for f in sorted(os.listdir(OUT)):
         print(f, os.path.getsize(os.path.join(OUT, f)))
 

@@ -47,6 +47,21 @@ def test_graph_fixtures(engine, name, conf, pol):
     assert abs(r["scores"][0, 0] - float(z["score"])) < 2 * TOL * float(z["score"])
 
 
+@pytest.mark.parametrize("tag", ["plain_", "conf_"])
+def test_run_instance_fixture_with_shuffled_columns(engine, tag):
+    """The reference's run_CGNN_tf / run_CGNN_confounders_tf on a DataFrame with shuffled columns, through the
+    host layer's plan and the graph kernel."""
+    import cgnn_b200.utils.Graph as my_graph
+    from test_golden_reference import run_instance_case
+    z = np.load(os.path.join(GOLD, "ref_shim_run_instance.npz"))
+    plan, data, noise, theta0, h, tr, te = run_instance_case(z, tag, my_graph)
+    r = engine.run_graph(data.astype(np.float32), [plan], n_runs=1, noise=noise[None].astype(np.float32),
+                         init_params=theta0[None].astype(np.float32), want_trace=True, h_layer_dim=h,
+                         train_epochs=tr, test_epochs=te, trace_every=1)
+    assert relerr(r["trace"][0], z[tag + "losses"]) < 2 * TOL
+    assert abs(r["scores"][0, 0] - float(z[tag + "score"])) < 2 * TOL * float(z[tag + "score"])
+
+
 def test_graph_fourier_fixture(engine):
     """The graph kernel in random-feature mode against the reference's CGNN_tf(use_Fast_MMD=True): the training
     losses with the rp() matrices the reference drew (2e-4: the fp32 floor of this loss, tests/test_pairwise_gpu.py)."""

@@ -89,6 +89,39 @@ def test_fourier_loss_and_fast_mmd_generator():
     assert abs(score - float(z["f_score"])) < TIGHT * score
 
 
+def run_instance_case(z, tag, graph_mod):
+    """(plan, data, noise in the engine's column ids, theta0, h, tr, te) of one case of ref_shim_run_instance.npz.
+    The plan comes from cgnn_b200.plan.build_plan with the DataFrame's (shuffled) column order."""
+    from cgnn_b200.plan import build_plan
+    conf = tag == "conf_"
+    sub = {k: z[tag + k] for k in ("edges", "weights", "skeleton")}
+    g = graph_from_fixture(sub, graph_mod)
+    plan = build_plan(g, columns=z[tag + "columns"].tolist(), confounders=conf)
+    own, shared = z[tag + "own_noise"], z[tag + "shared_noise"]
+    steps, n_var, n = own.shape
+    noise = np.zeros((steps, plan["n_noise"], n))
+    for pos, nd in enumerate(plan["nodes"]):
+        noise[:, nd["noise"][0]] = own[:, pos]
+    for e in range(shared.shape[1]):
+        noise[:, n_var + e] = shared[:, e]
+    return plan, z[tag + "data"], noise, z[tag + "theta0"], int(z[tag + "h"]), int(z[tag + "train"]), int(z[tag + "test"])
+
+
+def test_run_instance_entry_points_with_shuffled_columns():
+    """run_CGNN_tf / run_CGNN_confounders_tf of the reference on a DataFrame whose columns are not in node order:
+    the host layer's own column mapping (cgnn_b200/plan.py) must lead the oracle to the same numbers."""
+    import cgnn_b200.utils.Graph as my_graph
+    from oracle import cgnn as oc
+    z = np.load(os.path.join(GOLD, "ref_shim_run_instance.npz"))
+    for tag in ("plain_", "conf_"):
+        plan, data, noise, theta0, h, tr, te = run_instance_case(z, tag, my_graph)
+        assert plan["columns"] != plan["list_nodes"]
+        theta, losses, _ = oc.train(theta0, data.astype(np.float64), noise[:tr], plan, h)
+        score, ev = oc.evaluate(theta, data.astype(np.float64), noise[tr:], plan, h)
+        np.testing.assert_allclose(np.concatenate([losses, ev]), z[tag + "losses"], rtol=TIGHT)
+        assert abs(score - float(z[tag + "score"])) < TIGHT * score
+
+
 def test_graph_generator_with_the_random_feature_loss():
     """CGNN_tf(use_Fast_MMD=True) of the reference (CGNN.py:92-93): losses of every train and evaluate sess.run
     and the evaluate() mean, replayed by the oracle with the recorded noise and rp() matrices."""
