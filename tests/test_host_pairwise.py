@@ -76,6 +76,35 @@ def test_predict_dataset_batches_and_scores(fake, tmp_path):
     assert abs(cgnn.GNN().predict_proba(a3, b3, 3, nb_runs=3) - pred[3]) < 1e-12 and np.isfinite(one)
 
 
+def test_predictions_equal_the_reference_code_on_scripted_run_scores(fake, capsys):
+    """The reference's own GNN.predict_proba / predict_dataset (GNN.py:180-207, PairwiseModel.py:32-55), with
+    tf_run_instance replaced by the fake engine's per-run score function, against the host layer driven by the
+    fake engine: same standardisation, same averaging over runs, same (BA-AB)/(BA+AB)."""
+    if not refload.available():
+        pytest.skip("needs the reference tree (build container only)")
+    import cgnn_b200 as cgnn
+    from cgnn_b200.utils import CCEPC_PairsFileReader
+    ref = refload.load()
+    nb_runs = 4
+
+    def scripted_run_instance(m, idx, run, **kw):          # signature of tf_run_instance (GNN.py:135)
+        w = np.arange(m.shape[0]) % 7
+        uid = (idx * nb_runs + run) * 2
+        return [np.float32(pair_run_score(uid, float(np.dot(m[:, 0], w)))), np.float32(pair_run_score(uid + 1, float(np.dot(m[:, 1], w))))]
+
+    ref["GNN"].tf_run_instance = scripted_run_instance
+    ref["Settings"].SETTINGS.NB_RUNS, ref["Settings"].SETTINGS.NB_JOBS = nb_runs, 1     # predict_dataset takes no kwargs there
+    f = os.path.join(EX, "Example_pairwise_pairs.csv")
+    rdf = ref["Formats"].CCEPC_PairsFileReader(f, scale=True)
+    want = ref["GNN"].GNN(backend="TensorFlow").predict_dataset(rdf)
+    capsys.readouterr()
+    got = cgnn.GNN(backend="TensorFlow").predict_dataset(CCEPC_PairsFileReader(f, scale=True), nb_runs=nb_runs)
+    np.testing.assert_allclose(got, np.asarray(want, dtype=np.float64), rtol=0, atol=2e-7)
+    one = ref["GNN"].GNN(backend="TensorFlow").predict_proba(rdf["A"][2], rdf["B"][2], 2, nb_runs=nb_runs, nb_jobs=1)
+    capsys.readouterr()
+    assert abs(cgnn.GNN().predict_proba(rdf["A"][2], rdf["B"][2], 2, nb_runs=nb_runs) - one) < 2e-7
+
+
 def test_unknown_backend_raises():
     import cgnn_b200 as cgnn
     with pytest.raises(KeyError):
