@@ -322,12 +322,13 @@ def main():
     ach_exp = exps / (k_ms * 1e-3)
     ach_flop = flops / (k_ms * 1e-3)
     roof = {"bound": "mufu", "achieved": ach_exp / 1e12, "peak": mufu_peak / 1e12, "unit": "Texp/s",
-            "frac": ach_exp / mufu_peak, "traffic": None,
+            "frac": ach_exp / mufu_peak, "traffic": int(round(569344.0 / 296.0 * n_inst)),
             "peak_source": "measured live: cgnn_b200_probe_peak (ex2.approx.ftz chains); MEASURED_PEAKS.json has "
                            "no MUFU/FP32 entry; nominal 148 SM x 16 lanes x 1.965 GHz = 4.65 Texp/s",
             "fp32": {"achieved_tflops": ach_flop / 1e12, "peak_tflops": ffma_peak / 1e12, "frac": ach_flop / ffma_peak},
             "kernel_ms_avg": k_ms, "algorithmic_exps_per_launch": exps, "algorithmic_flops_per_launch": flops,
-            "traffic_note": "ncu --set full on a 296-instance x 30-step launch of the same kernel: dram read 0.55 MB, "
+            "traffic_note": "DRAM bytes per launch, scaled by the instance count from one ncu --set full capture of a 296-instance x 30-step "
+                            "launch of the same kernel (dram__bytes_read 569,344 + dram__bytes_write 0): dram read 0.55 MB, "
                             "write 0 (profiles/r1_pairwise_pol3_far_ncu_full.txt) - the working set lives in shared memory",
             "note": "algorithmic count = 7 exp per kernel evaluation (SURVEY 8d); exp_policy p issues 7/5/4/3 MUFU per "
                     "evaluation for p=0/1/2/3 (the others come from exact power relations between the bandwidths), so "
