@@ -3,7 +3,7 @@
 The shared library is the product; it is built here (cross-compiled, no GPU needed) and travels
 to the GPU box with the repository snapshot.  Translation units are compiled in parallel:
 capi.cu (pairwise path, life cycle, probes), graph_api.cu (graph path host side) and graph_inst.cu
-once per (padded column count, padded hidden width) pair (-DCGNN_DP=8|16|20|24|32 -DCGNN_HP=20|32).
+once per (padded column count, padded hidden width) pair (-DCGNN_DP=8|16|20|22|24|32 -DCGNN_HP=20|32).
 """
 import os
 import shutil
@@ -14,7 +14,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 OBJ = os.path.join(HERE, "build")
 LIB = os.path.join(HERE, "libcgnn_b200.so")
-GRAPH_DPS = (8, 16, 20, 24, 32)
+GRAPH_DPS = (8, 16, 20, 22, 24, 32)
 GRAPH_HPS = (20, 32)
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
               "-Xcompiler", "-fPIC"]

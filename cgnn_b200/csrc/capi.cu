@@ -44,6 +44,22 @@ __global__ void __launch_bounds__(512) probe_ffma_kernel(float* sink, int iters)
     if (s == 123.456f) sink[0] = s;
 }
 
+// packed FP32x2 FMA chains (fma.rn.f32x2): does the FMA pipe retire more than 128 FMA per clock per SM this way?
+__global__ void __launch_bounds__(512) probe_ffma2_kernel(float* sink, int iters) {
+    float2 x[8];
+    const float2 a = splat2(0.999f + 1e-6f * float(threadIdx.x & 31)), b = splat2(1e-3f);
+#pragma unroll
+    for (int k = 0; k < 8; ++k) x[k] = make_float2(0.1f * float(k + 1), 0.05f * float(k + 1));
+    for (int it = 0; it < iters; ++it) {
+#pragma unroll
+        for (int k = 0; k < 8; ++k) x[k] = ffma2(x[k], a, b);
+    }
+    float s = 0.f;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) s += x[k].x + x[k].y;
+    if (s == 123.456f) sink[0] = s;
+}
+
 template <int POL>
 static cudaError_t launch_pairwise(const PairwiseArgs& a, int grid, size_t smem, cudaStream_t st) {
     cudaError_t e = cudaFuncSetAttribute(pairwise_kernel<POL>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem));
@@ -287,7 +303,7 @@ int cgnn_b200_pairwise_step_debug(cgnn_ctx* ctx, const cgnn_hparams* hp, const f
 
 int cgnn_b200_probe_peak(cgnn_ctx* ctx, int kind, int reps, double* out_per_second) {
     if (!ctx || !out_per_second) return CGNN_ERR_ARG;
-    if (kind < 0 || kind > 1) return fail(ctx, CGNN_ERR_ARG, "probe kind %d unknown", kind);
+    if (kind < 0 || kind > 2) return fail(ctx, CGNN_ERR_ARG, "probe kind %d unknown", kind);
     CU(cudaSetDevice(ctx->device));
     int rc = ensure(ctx, ctx->counter, 256);
     if (rc) return rc;
@@ -295,14 +311,15 @@ int cgnn_b200_probe_peak(cgnn_ctx* ctx, int kind, int reps, double* out_per_seco
     double best = 0.0;
     for (int r = 0; r < std::max(reps, 1) + 1; ++r) {      // first launch is a warm-up
         CU(cudaEventRecord(ctx->ev0, ctx->stream));
-        if (kind == 0) probe_mufu_kernel<<<grid, nt, 0, ctx->stream>>>(static_cast<float*>(ctx->counter.p), iters);
-        else           probe_ffma_kernel<<<grid, nt, 0, ctx->stream>>>(static_cast<float*>(ctx->counter.p), iters);
+        if (kind == 0)      probe_mufu_kernel<<<grid, nt, 0, ctx->stream>>>(static_cast<float*>(ctx->counter.p), iters);
+        else if (kind == 1) probe_ffma_kernel<<<grid, nt, 0, ctx->stream>>>(static_cast<float*>(ctx->counter.p), iters);
+        else                probe_ffma2_kernel<<<grid, nt, 0, ctx->stream>>>(static_cast<float*>(ctx->counter.p), iters);
         CU(cudaGetLastError());
         CU(cudaEventRecord(ctx->ev1, ctx->stream));
         CU(cudaStreamSynchronize(ctx->stream));
         float ms = 0.f;
         CU(cudaEventElapsedTime(&ms, ctx->ev0, ctx->ev1));
-        const double ops = double(grid) * nt * double(iters) * 8.0 * (kind == 0 ? 1.0 : 2.0);
+        const double ops = double(grid) * nt * double(iters) * 8.0 * (kind == 0 ? 1.0 : kind == 1 ? 2.0 : 4.0);
         if (r > 0) best = std::max(best, ops / (double(ms) * 1e-3));
     }
     *out_per_second = best;

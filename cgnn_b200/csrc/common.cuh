@@ -261,6 +261,56 @@ __device__ __forceinline__ float2 ksum_p2(float2 Dp) {
 }
 
 // ---------------------------------------------------------------------------------------------
+// The same two-at-once chains on UNSCALED squared distances (graph kernel: its coordinates cannot be
+// prescaled for free, one FMUL2 turns the pair of distances into ex2 arguments instead):
+//   wsum = 50 k6 + G0 q + G1 k1 + p (G2 + p (G3 + p^2)) + G5 k5,   q = k(0.005), p = k(0.25), G4 = 1.
+// ---------------------------------------------------------------------------------------------
+template <int POL>
+__device__ __forceinline__ float2 wsum_r2(float2 D) {
+    const float2 q = ex2f2(fmul2(D, splat2(C0)));
+    const float2 p = ex2f2(fmul2(D, splat2(C2)));
+    float2 w = ex2f2(ffma2(D, splat2(C6), splat2(CGNN_LOG2_50)));               // 50 * k(50)
+    if (POL >= 2) {
+        const float2 q2 = fmul2(q, q), q4 = fmul2(q2, q2), q8 = fmul2(q4, q4);
+        w = ffma2(ffma2(splat2(G1), fmul2(q8, q), splat2(G0)), q, w);
+    } else {
+        w = ffma2(splat2(G1), ex2f2(fmul2(D, splat2(C1))), ffma2(splat2(G0), q, w));
+    }
+    if (POL >= 1) {
+        const float2 p2 = fmul2(p, p);
+        w = ffma2(ffma2(fadd2(p2, splat2(G3)), p, splat2(G2)), p, w);
+        if (POL >= 3) { const float2 p4 = fmul2(p2, p2), p8 = fmul2(p4, p4); w = ffma2(splat2(G5), fmul2(fmul2(p8, p8), p4), w); }
+        else w = ffma2(splat2(G5), ex2f2(fmul2(D, splat2(C5))), w);
+    } else {
+        w = ffma2(splat2(G2), p, w);
+        w = ffma2(splat2(G3), ex2f2(fmul2(D, splat2(C3))), w);
+        w = fadd2(w, ex2f2(fmul2(D, splat2(C4))));
+        w = ffma2(splat2(G5), ex2f2(fmul2(D, splat2(C5))), w);
+    }
+    return w;
+}
+
+template <int POL>
+__device__ __forceinline__ float2 ksum_r2(float2 D) {
+    const float2 q = ex2f2(fmul2(D, splat2(C0)));
+    const float2 p = ex2f2(fmul2(D, splat2(C2)));
+    float2 s = ex2f2(fmul2(D, splat2(C6)));
+    if (POL >= 2) { const float2 q2 = fmul2(q, q), q4 = fmul2(q2, q2), q5 = fmul2(q4, q); s = fadd2(s, ffma2(q5, q5, q)); }
+    else s = fadd2(s, fadd2(q, ex2f2(fmul2(D, splat2(C1)))));
+    if (POL >= 1) {
+        const float2 p2 = fmul2(p, p), p4 = fmul2(p2, p2);
+        float2 t = fadd2(ffma2(p2, p2, p2), p);                                  // p + p^2 + p^4
+        if (POL >= 3) { const float2 p8 = fmul2(p4, p4); t = ffma2(fmul2(p8, p8), p4, t); }
+        else t = fadd2(t, ex2f2(fmul2(D, splat2(C5))));
+        s = fadd2(s, t);
+    } else {
+        s = fadd2(s, fadd2(fadd2(p, ex2f2(fmul2(D, splat2(C3)))),
+                           fadd2(ex2f2(fmul2(D, splat2(C4))), ex2f2(fmul2(D, splat2(C5))))));
+    }
+    return s;
+}
+
+// ---------------------------------------------------------------------------------------------
 // Order-independent accumulation into shared memory: 64-bit fixed point (2^-36 resolution,
 // +-2^27 range) with native integer atomics.  Integer addition is associative, so the result does
 // not depend on warp scheduling: the engine is bit-reproducible run to run.

@@ -86,7 +86,7 @@ struct GraphArgs {
     float *dbg_loss, *dbg_pred, *dbg_dldp, *dbg_grad, *dbg_params;
     // random-feature ("Fourier") MMD, Loss.py:35-56: fast_k = nb_vectors_approx_MMD, 0 = Gaussian-kernel MMD
     int t_smem;                // 1: the observed matrix of the instance is copied to shared memory (it fits)
-    int t_ring;                // 1: it does not fit and is streamed through the warps' idle noise buffers (gr_mmd_train_row_ring)
+    int t_ring;                // 1: it does not fit and is streamed through the warps' idle noise buffers (GR_T_RING)
     int fast_k;
     const float* wz_ext;       // NULL or [n_inst][epochs][n_var+1][7*fast_k]: the matrix of Loss.py:35-37 per step
 };
@@ -175,69 +175,82 @@ __device__ __forceinline__ void gr_forward_block(const GrSmem& s, const float* n
 
 template <int DP>
 __device__ __forceinline__ void gr_load_col_smem(const float* __restrict__ base, int j, float (&t)[DP]) {
-    const float4* r = reinterpret_cast<const float4*>(base + size_t(j) * DP);
+    if constexpr (DP % 4 == 0) {
+        const float4* r = reinterpret_cast<const float4*>(base + size_t(j) * DP);
 #pragma unroll
-    for (int q = 0; q < DP / 4; ++q) { const float4 v = r[q]; t[4 * q] = v.x; t[4 * q + 1] = v.y; t[4 * q + 2] = v.z; t[4 * q + 3] = v.w; }
+        for (int q = 0; q < DP / 4; ++q) { const float4 v = r[q]; t[4 * q] = v.x; t[4 * q + 1] = v.y; t[4 * q + 2] = v.z; t[4 * q + 3] = v.w; }
+    } else {
+        const float2* r = reinterpret_cast<const float2*>(base + size_t(j) * DP);
+#pragma unroll
+        for (int q = 0; q < DP / 2; ++q) { const float2 v = r[q]; t[2 * q] = v.x; t[2 * q + 1] = v.y; }
+    }
 }
 template <int DP>
 __device__ __forceinline__ void gr_load_col_gmem(const float* __restrict__ base, int j, float (&t)[DP]) {
-    const float4* r = reinterpret_cast<const float4*>(base + size_t(j) * DP);
+    if constexpr (DP % 4 == 0) {
+        const float4* r = reinterpret_cast<const float4*>(base + size_t(j) * DP);
 #pragma unroll
-    for (int q = 0; q < DP / 4; ++q) { const float4 v = __ldg(r + q); t[4 * q] = v.x; t[4 * q + 1] = v.y; t[4 * q + 2] = v.z; t[4 * q + 3] = v.w; }
+        for (int q = 0; q < DP / 4; ++q) { const float4 v = __ldg(r + q); t[4 * q] = v.x; t[4 * q + 1] = v.y; t[4 * q + 2] = v.z; t[4 * q + 3] = v.w; }
+    } else {
+        const float2* r = reinterpret_cast<const float2*>(base + size_t(j) * DP);
+#pragma unroll
+        for (int q = 0; q < DP / 2; ++q) { const float2 v = __ldg(r + q); t[2 * q] = v.x; t[2 * q + 1] = v.y; }
+    }
 }
 
-// squared distance of this row to column t (DP floats as DP/2 pairs) - four partial sums, packed
-template <int DP>
-__device__ __forceinline__ float gr_sqdist(const float2 (&p)[DP / 2], const float (&t)[DP], float2 (&df)[DP / 2]) {
-    float2 Da = make_float2(0.f, 0.f), Db = make_float2(0.f, 0.f);
+// one row (DP floats) as DP/2 register pairs; widest aligned loads the row stride allows (DP = 22: 8-byte)
+template <int DP, bool GMEM>
+__device__ __forceinline__ void gr_load_pairs(const float* __restrict__ row, float2 (&t)[DP / 2]) {
+    if constexpr (DP % 4 == 0) {
+        const float4* r = reinterpret_cast<const float4*>(row);
+#pragma unroll
+        for (int q = 0; q < DP / 4; ++q) {
+            const float4 v = GMEM ? __ldg(r + q) : r[q];
+            t[2 * q] = make_float2(v.x, v.y); t[2 * q + 1] = make_float2(v.z, v.w);
+        }
+    } else {
+        const float2* r = reinterpret_cast<const float2*>(row);
+#pragma unroll
+        for (int q = 0; q < DP / 2; ++q) t[q] = GMEM ? __ldg(r + q) : r[q];
+    }
+}
+
+// where the observed rows of the MMD passes come from
+enum : int { GR_T_GMEM = 0, GR_T_SMEM = 1, GR_T_RING = 2 };
+
+// ---- gradient pass ---------------------------------------------------------------------------------------
+// This lane's row is held NEGATED (np = -P_i), so a difference is one FADD2 per coordinate pair: d = X_j - P_i.
+// One iteration takes the observed column j AND the generated column j: the two squared distances go through
+// the kernel-weight chain as one register pair (FMUL2 / FFMA2, wsum_r2), and the two contributions
+//     acc += w(P_i,T_j) (T_j - P_i) - w(P_i,P_j) (P_j - P_i)          ( = - dLoss/dP_i * N^2/4, accumulated )
+// cancel as they are added - the running sum stays at the size of the (small) result for the whole sweep, which
+// is what lets ONE fp32 accumulator per coordinate replace the former two-level sum (tools/expansion_error_model.py
+// measures 7e-7 at the trained state of the 22-variable example).
+template <int DP, int POL, bool TG>
+__device__ __forceinline__ void gr_grad_pair(const float2 (&np)[DP / 2], const float* __restrict__ tj,
+                                             const float* __restrict__ pj, float2 (&acc)[DP / 2]) {
+    float2 d0[DP / 2], d1[DP / 2];
+    gr_load_pairs<DP, TG>(tj, d0);
+    gr_load_pairs<DP, false>(pj, d1);
+    float2 e0a = make_float2(0.f, 0.f), e0b = e0a, e1a = e0a, e1b = e0a;
 #pragma unroll
     for (int q = 0; q < DP / 2; ++q) {
-        df[q] = fsub2(p[q], make_float2(t[2 * q], t[2 * q + 1]));
-        if (q & 1) Db = ffma2(df[q], df[q], Db); else Da = ffma2(df[q], df[q], Da);
+        d0[q] = fadd2(d0[q], np[q]);
+        d1[q] = fadd2(d1[q], np[q]);
+        if (q & 1) { e0b = ffma2(d0[q], d0[q], e0b); e1b = ffma2(d1[q], d1[q], e1b); }
+        else       { e0a = ffma2(d0[q], d0[q], e0a); e1a = ffma2(d1[q], d1[q], e1a); }
     }
-    const float2 D = fadd2(Da, Db);
-    return D.x + D.y;
-}
-
-// MMD gradient of one row: tot[c] = sum_j w(P_i,T_j)(P_ic - T_jc) - sum_j w(P_i,P_j)(P_ic - P_jc)   (unscaled)
-// fp32 accumulation in runs of one PT tile + one PP tile (64 evaluations), then a second-level fp32 sum
-// of the (mutually cancelling, hence small) tile pairs.  All column-wise arithmetic is FFMA2/FADD2.
-template <int DP, int POL, bool TS>
-__device__ __forceinline__ void gr_mmd_train_row(const float* __restrict__ Pm, const float* __restrict__ T, int N,
-                                                 const float2 (&p)[DP / 2], float2 (&tot)[DP / 2]) {
+    const float2 e0 = fadd2(e0a, e0b), e1 = fadd2(e1a, e1b);
+    const float2 w = wsum_r2<POL>(make_float2(e0.x + e0.y, e1.x + e1.y));
+    const float2 w0 = splat2(w.x), w1 = splat2(-w.y);
 #pragma unroll
-    for (int q = 0; q < DP / 2; ++q) tot[q] = make_float2(0.f, 0.f);
-    for (int j0 = 0; j0 < N; j0 += 32) {
-        const int j1 = min(j0 + 32, N);
-        float2 acc[DP / 2];
-#pragma unroll
-        for (int q = 0; q < DP / 2; ++q) acc[q] = make_float2(0.f, 0.f);
-        for (int j = j0; j < j1; ++j) {
-            float t[DP];
-            float2 df[DP / 2];
-            if (TS) gr_load_col_smem<DP>(T, j, t); else gr_load_col_gmem<DP>(T, j, t);
-            const float2 w = splat2(wsum<POL>(gr_sqdist<DP>(p, t, df)));
-#pragma unroll
-            for (int q = 0; q < DP / 2; ++q) acc[q] = ffma2(w, df[q], acc[q]);
-        }
-        for (int j = j0; j < j1; ++j) {
-            float t[DP];
-            float2 df[DP / 2];
-            gr_load_col_smem<DP>(Pm, j, t);
-            const float2 w = splat2(-wsum<POL>(gr_sqdist<DP>(p, t, df)));
-#pragma unroll
-            for (int q = 0; q < DP / 2; ++q) acc[q] = ffma2(w, df[q], acc[q]);
-        }
-#pragma unroll
-        for (int q = 0; q < DP / 2; ++q) tot[q] = fadd2(tot[q], acc[q]);
-    }
+    for (int q = 0; q < DP / 2; ++q) acc[q] = ffma2(w1, d1[q], ffma2(w0, d0[q], acc[q]));
 }
 
 // ---- observed matrix streamed through a per-warp ring (shapes whose observed matrix does not fit shared memory) --
 // The warp's noise buffer is idle while the warp walks the observed rows, and it holds at least 32 rows whenever
 // nn_pad >= DP: two halves of GR_RING_H rows, filled with cp.async one half ahead of the arithmetic, replace
-// the L1/L2 round trip of every row by a shared-memory broadcast read.  Same order of operations as
-// gr_mmd_train_row / gr_mmd_eval_cols.
+// the L1/L2 round trip of every row by a shared-memory broadcast read.
 constexpr int GR_RING_H = 16;
 
 __device__ __forceinline__ void gr_cp_async16(void* dst_smem, const void* src) {
@@ -259,51 +272,64 @@ __device__ __forceinline__ void gr_ring_wait() {            // everything but th
     __syncwarp();
 }
 
-template <int DP, int POL>
-__device__ __forceinline__ void gr_mmd_train_row_ring(const float* __restrict__ Pm, const float* __restrict__ T, float* ring, int N,
-                                                      int lane, const float2 (&p)[DP / 2], float2 (&tot)[DP / 2]) {
-    const int n_chunks = (N + GR_RING_H - 1) / GR_RING_H;
+// dLoss/dP_i (unscaled, negated) of this lane's row over all N observed and generated columns
+template <int DP, int POL, int TM>
+__device__ __forceinline__ void gr_mmd_grad_row(const float* __restrict__ Pm, const float* __restrict__ T, float* ring, int N,
+                                                int lane, const float2 (&np)[DP / 2], float2 (&acc)[DP / 2]) {
 #pragma unroll
-    for (int q = 0; q < DP / 2; ++q) tot[q] = make_float2(0.f, 0.f);
-    gr_ring_issue<DP>(T, ring, 0, n_chunks, lane);
-    for (int j0 = 0; j0 < N; j0 += 32) {
-        const int j1 = min(j0 + 32, N);
-        float2 acc[DP / 2];
-#pragma unroll
-        for (int q = 0; q < DP / 2; ++q) acc[q] = make_float2(0.f, 0.f);
-        for (int c = j0 / GR_RING_H; c * GR_RING_H < j1; ++c) {
+    for (int q = 0; q < DP / 2; ++q) acc[q] = make_float2(0.f, 0.f);
+    if constexpr (TM == GR_T_RING) {
+        const int n_chunks = (N + GR_RING_H - 1) / GR_RING_H;
+        gr_ring_issue<DP>(T, ring, 0, n_chunks, lane);
+        for (int c = 0; c < n_chunks; ++c) {
             gr_ring_issue<DP>(T, ring, c + 1, n_chunks, lane);
             gr_ring_wait();
             const float* B = ring + (c & 1) * GR_RING_H * DP;
-            const int n = min(GR_RING_H, j1 - c * GR_RING_H);
-            for (int j = 0; j < n; ++j) {
-                float t[DP];
-                float2 df[DP / 2];
-                gr_load_col_smem<DP>(B, j, t);
-                const float2 w = splat2(wsum<POL>(gr_sqdist<DP>(p, t, df)));
-#pragma unroll
-                for (int q = 0; q < DP / 2; ++q) acc[q] = ffma2(w, df[q], acc[q]);
-            }
+            const float* Pc = Pm + size_t(c) * GR_RING_H * DP;
+            const int n = min(GR_RING_H, N - c * GR_RING_H);
+            for (int j = 0; j < n; ++j) gr_grad_pair<DP, POL, false>(np, B + j * DP, Pc + j * DP, acc);
             __syncwarp();                                   // the half may be refilled two chunks later
         }
-        for (int j = j0; j < j1; ++j) {
-            float t[DP];
-            float2 df[DP / 2];
-            gr_load_col_smem<DP>(Pm, j, t);
-            const float2 w = splat2(-wsum<POL>(gr_sqdist<DP>(p, t, df)));
-#pragma unroll
-            for (int q = 0; q < DP / 2; ++q) acc[q] = ffma2(w, df[q], acc[q]);
-        }
-#pragma unroll
-        for (int q = 0; q < DP / 2; ++q) tot[q] = fadd2(tot[q], acc[q]);
+        asm volatile("cp.async.wait_group 0;" ::: "memory");
+        __syncwarp();
+    } else {
+        for (int j = 0; j < N; ++j) gr_grad_pair<DP, POL, TM == GR_T_GMEM>(np, T + size_t(j) * DP, Pm + size_t(j) * DP, acc);
     }
-    asm volatile("cp.async.wait_group 0;" ::: "memory");
-    __syncwarp();
 }
 
-// sum_j k(R_i, T_j) over all N observed rows, fp32 runs of 64 then fp64 (as gr_mmd_eval_cols)
+// ---- loss passes -----------------------------------------------------------------------------------------
+// kernel sums of two columns at once (packed chain): (sum_g k_g(P_i, A), sum_g k_g(P_i, B))
+template <int DP, int POL, bool GMEM>
+__device__ __forceinline__ float2 gr_k_pair(const float2 (&np)[DP / 2], const float* __restrict__ ca, const float* __restrict__ cb) {
+    float2 d0[DP / 2], d1[DP / 2];
+    gr_load_pairs<DP, GMEM>(ca, d0);
+    gr_load_pairs<DP, GMEM>(cb, d1);
+    float2 e0a = make_float2(0.f, 0.f), e0b = e0a, e1a = e0a, e1b = e0a;
+#pragma unroll
+    for (int q = 0; q < DP / 2; ++q) {
+        d0[q] = fadd2(d0[q], np[q]);
+        d1[q] = fadd2(d1[q], np[q]);
+        if (q & 1) { e0b = ffma2(d0[q], d0[q], e0b); e1b = ffma2(d1[q], d1[q], e1b); }
+        else       { e0a = ffma2(d0[q], d0[q], e0a); e1a = ffma2(d1[q], d1[q], e1a); }
+    }
+    const float2 e0 = fadd2(e0a, e0b), e1 = fadd2(e1a, e1b);
+    return ksum_r2<POL>(make_float2(e0.x + e0.y, e1.x + e1.y));
+}
+
+// sum_j k(R_i, B_j) over n consecutive rows starting at B (n <= 64): one fp32 run
+template <int DP, int POL, bool GMEM>
+__device__ __forceinline__ float gr_k_run(const float* __restrict__ B, int n, const float2 (&np)[DP / 2]) {
+    float2 acc = make_float2(0.f, 0.f);
+    int j = 0;
+    for (; j + 1 < n; j += 2) acc = fadd2(acc, gr_k_pair<DP, POL, GMEM>(np, B + size_t(j) * DP, B + size_t(j + 1) * DP));
+    float r = acc.x + acc.y;
+    if (j < n) r += gr_k_pair<DP, POL, GMEM>(np, B + size_t(j) * DP, B + size_t(j) * DP).x;
+    return r;
+}
+
+// sum_j k(R_i, T_j) over all N observed rows through the ring, fp32 runs of 64 then fp64 (as gr_mmd_eval_cols)
 template <int DP, int POL>
-__device__ __forceinline__ double gr_mmd_eval_row_ring(const float* __restrict__ T, float* ring, int N, int lane, const float2 (&p)[DP / 2]) {
+__device__ __forceinline__ double gr_mmd_eval_row_ring(const float* __restrict__ T, float* ring, int N, int lane, const float2 (&np)[DP / 2]) {
     const int n_chunks = (N + GR_RING_H - 1) / GR_RING_H;
     double tot = 0.0;
     gr_ring_issue<DP>(T, ring, 0, n_chunks, lane);
@@ -313,15 +339,7 @@ __device__ __forceinline__ double gr_mmd_eval_row_ring(const float* __restrict__
         for (int c = j0 / GR_RING_H; c * GR_RING_H < j1; ++c) {
             gr_ring_issue<DP>(T, ring, c + 1, n_chunks, lane);
             gr_ring_wait();
-            const float* B = ring + (c & 1) * GR_RING_H * DP;
-            const int n = min(GR_RING_H, j1 - c * GR_RING_H);
-#pragma unroll 2
-            for (int j = 0; j < n; ++j) {
-                float t[DP];
-                float2 df[DP / 2];
-                gr_load_col_smem<DP>(B, j, t);
-                acc += ksum<POL>(gr_sqdist<DP>(p, t, df));
-            }
+            acc += gr_k_run<DP, POL, false>(ring + (c & 1) * GR_RING_H * DP, min(GR_RING_H, j1 - c * GR_RING_H), np);
             __syncwarp();
         }
         tot += double(acc);
@@ -331,27 +349,17 @@ __device__ __forceinline__ double gr_mmd_eval_row_ring(const float* __restrict__
     return tot;
 }
 
-// Loss share of one row: sum_j [ k(R_i, B_j) ] over columns [c0, c1) of a source (smem or gmem), fp64 across tiles.
+// Loss share of one row: sum_j [ k(R_i, B_j) ] over columns [c0, c1) of a source (smem or gmem), fp64 across runs of 64.
 template <int DP, int POL, bool GMEM>
-__device__ __forceinline__ double gr_mmd_eval_cols(const float* __restrict__ B, int c0, int c1, const float2 (&p)[DP / 2]) {
+__device__ __forceinline__ double gr_mmd_eval_cols(const float* __restrict__ B, int c0, int c1, const float2 (&np)[DP / 2]) {
     double tot = 0.0;
-    for (int j0 = c0; j0 < c1; j0 += 64) {
-        const int j1 = min(j0 + 64, c1);
-        float acc = 0.f;
-#pragma unroll 2
-        for (int j = j0; j < j1; ++j) {
-            float t[DP];
-            float2 df[DP / 2];
-            if (GMEM) gr_load_col_gmem<DP>(B, j, t); else gr_load_col_smem<DP>(B, j, t);
-            acc += ksum<POL>(gr_sqdist<DP>(p, t, df));
-        }
-        tot += double(acc);
-    }
+    for (int j0 = c0; j0 < c1; j0 += 64)
+        tot += double(gr_k_run<DP, POL, GMEM>(B + size_t(j0) * DP, min(64, c1 - j0), np));
     return tot;
 }
 template <int DP, int POL, bool GMEM>
-__device__ __forceinline__ double gr_mmd_eval_row(const float* __restrict__ B, int N, const float2 (&p)[DP / 2]) {
-    return gr_mmd_eval_cols<DP, POL, GMEM>(B, 0, N, p);
+__device__ __forceinline__ double gr_mmd_eval_row(const float* __restrict__ B, int N, const float2 (&np)[DP / 2]) {
+    return gr_mmd_eval_cols<DP, POL, GMEM>(B, 0, N, np);
 }
 
 // Same for a block of the SAME set as the rows (pred-pred, true-true): the kernel matrix is symmetric, so
@@ -361,14 +369,14 @@ __device__ __forceinline__ int gr_npp(int I, int NB) {
     return (NB & 1) ? (NB - 1) / 2 : (NB / 2 - 1 + (I < NB / 2 ? 1 : 0));
 }
 template <int DP, int POL, bool GMEM>
-__device__ __forceinline__ double gr_mmd_eval_row_sym(const float* __restrict__ B, int N, int NB, int rb, const float2 (&p)[DP / 2]) {
-    double tot = gr_mmd_eval_cols<DP, POL, GMEM>(B, 32 * rb, min(32 * rb + 32, N), p);
+__device__ __forceinline__ double gr_mmd_eval_row_sym(const float* __restrict__ B, int N, int NB, int rb, const float2 (&np)[DP / 2]) {
+    double tot = gr_mmd_eval_cols<DP, POL, GMEM>(B, 32 * rb, min(32 * rb + 32, N), np);
     const int npp = gr_npp(rb, NB);
     double off = 0.0;
     for (int q = 0; q < npp; ++q) {
         int J = rb + 1 + q;
         if (J >= NB) J -= NB;
-        off += gr_mmd_eval_cols<DP, POL, GMEM>(B, 32 * J, min(32 * J + 32, N), p);
+        off += gr_mmd_eval_cols<DP, POL, GMEM>(B, 32 * J, min(32 * J + 32, N), np);
     }
     return tot + 2.0 * off;
 }
@@ -578,6 +586,9 @@ __global__ void __launch_bounds__(GR_NT, 1) graph_kernel(const GraphArgs a) {
     cg::cluster_group cl = cg::this_cluster();
     const int csz = int(cl.num_blocks()), crank = int(cl.block_rank());
     const int rb0 = crank + csz * warp, rbs = csz * GR_NW;        // this warp's row blocks of the MMD passes
+    // one row block per warp, same warp in the forward and the backward pass, noise buffer not lent to the ring:
+    // the noise the forward pass drew is still there when the backward pass needs it
+    const bool noise_kept = csz == 1 && NB <= GR_NW && !a.t_ring;
 
     GrSmem s;
     {
@@ -660,11 +671,10 @@ __global__ void __launch_bounds__(GR_NT, 1) graph_kernel(const GraphArgs a) {
             double part = 0.0;
             for (int rb = rb0; rb < NB; rb += rbs) {
                 const int i = 32 * rb + lane;
-                float pf[DP];
-                float2 p[DP / 2];
-                gr_load_col_gmem<DP>(T, min(i, N - 1), pf);
+                float2 p[DP / 2];                                // the row, negated (see gr_grad_pair)
+                gr_load_pairs<DP, true>(T + size_t(min(i, N - 1)) * DP, p);
 #pragma unroll
-                for (int q = 0; q < DP / 2; ++q) p[q] = make_float2(pf[2 * q], pf[2 * q + 1]);
+                for (int q = 0; q < DP / 2; ++q) p[q] = make_float2(-p[q].x, -p[q].y);
                 const double v = gr_mmd_eval_row_sym<DP, POL, true>(T, N, NB, rb, p);
                 if (i < N) part += v;
             }
@@ -744,7 +754,7 @@ __global__ void __launch_bounds__(GR_NT, 1) graph_kernel(const GraphArgs a) {
                 if (a.dbg_dldp && has && i < N)
                     for (int c = 0; c < s.desc->n_var; ++c) a.dbg_dldp[(size_t(it) * N + i) * s.desc->n_var + c] = gl[c];
                 if (has) {
-                    gr_fill_noise(s, a, nb, i, lane, it, uid, key, noise_step);
+                    if (!noise_kept) gr_fill_noise(s, a, nb, i, lane, it, uid, key, noise_step);
                     gr_backward_block<DP, HP>(s, nb, i, lane, gl);
                     __syncwarp();
                 }
@@ -755,11 +765,10 @@ __global__ void __launch_bounds__(GR_NT, 1) graph_kernel(const GraphArgs a) {
                     double part = 0.0;
                     for (int rb = rb0; rb < NB; rb += rbs) {
                         const int i = 32 * rb + lane;
-                        float pf[DP];
                         float2 p[DP / 2];
-                        gr_load_col_smem<DP>(s.Pm, i, pf);
+                        gr_load_pairs<DP, false>(s.Pm + size_t(i) * DP, p);
     #pragma unroll
-                        for (int q = 0; q < DP / 2; ++q) p[q] = make_float2(pf[2 * q], pf[2 * q + 1]);
+                        for (int q = 0; q < DP / 2; ++q) p[q] = make_float2(-p[q].x, -p[q].y);
                         const double v = gr_mmd_eval_row_sym<DP, POL, false>(s.Pm, N, NB, rb, p) -
                                          2.0 * (a.t_smem ? gr_mmd_eval_row<DP, POL, false>(s.Ts, N, p)
                                                 : a.t_ring ? gr_mmd_eval_row_ring<DP, POL>(T, nb, N, lane, p) : gr_mmd_eval_row<DP, POL, true>(T, N, p));
@@ -781,23 +790,22 @@ __global__ void __launch_bounds__(GR_NT, 1) graph_kernel(const GraphArgs a) {
                     const int i = 32 * rb + lane;
                     float gl[DP];
                     {
-                        float pf[DP];
                         float2 p[DP / 2], tot[DP / 2];
-                        gr_load_col_smem<DP>(s.Pm, i, pf);
+                        gr_load_pairs<DP, false>(s.Pm + size_t(i) * DP, p);
     #pragma unroll
-                        for (int q = 0; q < DP / 2; ++q) p[q] = make_float2(pf[2 * q], pf[2 * q + 1]);
-                        if (a.t_smem) gr_mmd_train_row<DP, POL, true>(s.Pm, s.Ts, N, p, tot);
-                        else if (a.t_ring) gr_mmd_train_row_ring<DP, POL>(s.Pm, T, nb, N, lane, p, tot);
-                        else gr_mmd_train_row<DP, POL, false>(s.Pm, T, N, p, tot);
+                        for (int q = 0; q < DP / 2; ++q) p[q] = make_float2(-p[q].x, -p[q].y);
+                        if (a.t_smem) gr_mmd_grad_row<DP, POL, GR_T_SMEM>(s.Pm, s.Ts, nb, N, lane, p, tot);
+                        else if (a.t_ring) gr_mmd_grad_row<DP, POL, GR_T_RING>(s.Pm, T, nb, N, lane, p, tot);
+                        else gr_mmd_grad_row<DP, POL, GR_T_GMEM>(s.Pm, T, nb, N, lane, p, tot);
     #pragma unroll
-                        for (int q = 0; q < DP / 2; ++q) {
-                            gl[2 * q] = (i < N) ? tot[q].x * scale : 0.f;
-                            gl[2 * q + 1] = (i < N) ? tot[q].y * scale : 0.f;
+                        for (int q = 0; q < DP / 2; ++q) {                   // tot holds the negated sum
+                            gl[2 * q] = (i < N) ? tot[q].x * -scale : 0.f;
+                            gl[2 * q + 1] = (i < N) ? tot[q].y * -scale : 0.f;
                         }
                     }
                     if (a.dbg_dldp && i < N)
                         for (int c = 0; c < s.desc->n_var; ++c) a.dbg_dldp[(size_t(it) * N + i) * s.desc->n_var + c] = gl[c];
-                    gr_fill_noise(s, a, nb, i, lane, it, uid, key, noise_step);
+                    if (!noise_kept) gr_fill_noise(s, a, nb, i, lane, it, uid, key, noise_step);
                     gr_backward_block<DP, HP>(s, nb, i, lane, gl);
                     __syncwarp();
                 }

@@ -25,13 +25,16 @@ static __global__ void gather_rows_kernel(const float* __restrict__ data, int n_
 #define DECL(DP_)                                                                                  \
     cudaError_t cgnn_launch_graph_dp##DP_##_hp20(int, const GraphArgs&, int, int, size_t, cudaStream_t, int*); \
     cudaError_t cgnn_launch_graph_dp##DP_##_hp32(int, const GraphArgs&, int, int, size_t, cudaStream_t, int*);
-DECL(8) DECL(16) DECL(20) DECL(24) DECL(32)
+DECL(8) DECL(16) DECL(20) DECL(22) DECL(24) DECL(32)
 #undef DECL
 
-static int pick_dp(int n_var) {
-    const int choices[5] = {8, 16, 20, 24, 32};
+// padded column count of the generated / observed matrices.  22 (the bundled example's width) has rows of 88 bytes:
+// 8-byte vector loads instead of 16-byte ones, but 11 instead of 12 coordinate pairs in every FFMA2 loop; the
+// random-feature mode keeps 16-byte rows (its frequency table is read with 128-bit loads).
+static int pick_dp(int n_var, bool fast) {
+    const int choices[6] = {8, 16, 20, 22, 24, 32};
     for (int c : choices)
-        if (n_var <= c) return c;
+        if (n_var <= c && !(fast && c == 22)) return c;
     return 0;
 }
 
@@ -41,7 +44,7 @@ static cudaError_t launch_graph(int dp, int hp, int pol, const GraphArgs& a, int
     case DP_:                                                                                                  \
         return hp == 20 ? cgnn_launch_graph_dp##DP_##_hp20(pol, a, n_clusters, csz, smem, st, max_clusters)    \
                         : cgnn_launch_graph_dp##DP_##_hp32(pol, a, n_clusters, csz, smem, st, max_clusters);
-    switch (dp) { CASE(8) CASE(16) CASE(20) CASE(24) CASE(32) }
+    switch (dp) { CASE(8) CASE(16) CASE(20) CASE(22) CASE(24) CASE(32) }
 #undef CASE
     return cudaErrorInvalidValue;
 }
@@ -118,7 +121,7 @@ static int run_graph_impl(cgnn_ctx* ctx, const cgnn_hparams* hp, const float* da
     if ((init_params || params_out) && ld_params < p_max)
         return fail(ctx, CGNN_ERR_ARG, "ld_params=%d smaller than the largest parameter count %d", ld_params, p_max);
 
-    const int DP = pick_dp(n_var);
+    const int DP = pick_dp(n_var, hp->fast_mmd_vectors > 0);
     const int NP = 32 * ((n_rows + 31) / 32);
     GraphArgs a{};
     const void* dp = nullptr;

@@ -95,9 +95,9 @@ class Engine:
         self._check(self._lib.cgnn_b200_set_stream(self._h, C.c_void_p(cuda_stream_ptr)), "set_stream")
 
     def probe_peak(self, kind, reps=5):
-        """kind 'mufu' -> exp/s, 'ffma' -> flop/s of this chip's pipes (micro-benchmark)."""
+        """kind 'mufu' -> exp/s, 'ffma' / 'ffma2' -> flop/s of scalar / packed (FP32x2) FMA chains (micro-benchmarks)."""
         out = C.c_double()
-        k = {"mufu": 0, "ffma": 1}[kind]
+        k = {"mufu": 0, "ffma": 1, "ffma2": 2}[kind]
         self._check(self._lib.cgnn_b200_probe_peak(self._h, k, reps, C.byref(out)), "probe_peak")
         return out.value
 

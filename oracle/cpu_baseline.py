@@ -13,38 +13,50 @@ import time
 import numpy as np
 
 
-def _one_instance(data, h, train_steps, eval_steps, seed):
+def _one_instance(data, h, train_steps, eval_steps, seed, repeats=1, warmup_steps=1):
+    """One worker process: `warmup_steps` untimed train steps (first-call costs of torch / autograd), then
+    `repeats` timed blocks of train_steps + eval_steps.  Returns [(train_s, eval_s)] per block and the last score."""
     import torch
     torch.set_num_threads(1)
     from . import gnn
     rng = np.random.default_rng(seed)
     n = data.shape[0]
-    theta0 = (0.05 * rng.normal(size=gnn.n_params(h))).astype(np.float32)
-    ntr = rng.normal(size=(train_steps, n)).astype(np.float32)
-    nev = rng.normal(size=(eval_steps, n)).astype(np.float32)
-    t0 = time.perf_counter()
-    theta, _, _ = gnn.train(theta0, data.astype(np.float32), ntr, h, dtype=torch.float32)
-    t1 = time.perf_counter()
-    score, _ = gnn.evaluate(theta, data.astype(np.float32), nev, h, dtype=torch.float32)
-    t2 = time.perf_counter()
-    return t1 - t0, t2 - t1, score
+    d32 = data.astype(np.float32)
+    theta = (0.05 * rng.normal(size=gnn.n_params(h))).astype(np.float32)
+    if warmup_steps > 0:
+        gnn.train(theta, d32, rng.normal(size=(warmup_steps, n)).astype(np.float32), h, dtype=torch.float32)
+    blocks, score = [], float("nan")
+    for _ in range(repeats):
+        ntr = rng.normal(size=(train_steps, n)).astype(np.float32)
+        nev = rng.normal(size=(eval_steps, n)).astype(np.float32)
+        t0 = time.perf_counter()
+        theta, _, _ = gnn.train(theta, d32, ntr, h, dtype=torch.float32)
+        t1 = time.perf_counter()
+        score, _ = gnn.evaluate(theta, d32, nev, h, dtype=torch.float32)
+        t2 = time.perf_counter()
+        blocks.append((t1 - t0, t2 - t1))
+    return blocks, score
 
 
-def time_pairwise_sample(data, h=30, n_instances=None, train_steps=8, eval_steps=4, n_jobs=None):
-    """Runs n_instances independent (train_steps + eval_steps)-step instances over n_jobs processes.
-    Returns dict(train_steps_per_s, wall_s, cores, sample)."""
+def time_pairwise_sample(data, h=30, n_instances=None, train_steps=3, eval_steps=2, n_jobs=None, repeats=3,
+                         warmup_steps=1):
+    """n_instances independent instances over n_jobs processes, each timing `repeats` blocks of
+    (train_steps + eval_steps) steps after an untimed warm-up.  Per block the per-step costs are averaged over the
+    workers; the caller turns them into a throughput and takes the median over the blocks.
+    Returns dict(blocks=[(per_train_step_s, per_eval_step_s)], per_train_step_s, per_eval_step_s (medians), ...)."""
     from joblib import Parallel, delayed
     n_jobs = n_jobs or os.cpu_count() or 1
     n_instances = n_instances or n_jobs
     t0 = time.perf_counter()
-    res = Parallel(n_jobs=n_jobs)(delayed(_one_instance)(data, h, train_steps, eval_steps, 1000 + k)
+    res = Parallel(n_jobs=n_jobs)(delayed(_one_instance)(data, h, train_steps, eval_steps, 1000 + k, repeats, warmup_steps)
                                   for k in range(n_instances))
     wall = time.perf_counter() - t0
-    ttr = sum(r[0] for r in res)
-    tev = sum(r[1] for r in res)
-    # throughput in the benchmark's unit: train steps per second of a job whose instances carry the
-    # same train:eval mix as the real workload (1000:500) - scale the measured per-step costs.
-    per_train = ttr / (n_instances * train_steps)
-    per_eval = tev / max(1, n_instances * eval_steps)
-    return dict(per_train_step_s=per_train, per_eval_step_s=per_eval, wall_s=wall, cores=n_jobs,
-                n_instances=n_instances, train_steps=train_steps, eval_steps=eval_steps)
+    blocks = []
+    for r in range(repeats):
+        ttr = sum(b[0][r][0] for b in res)
+        tev = sum(b[0][r][1] for b in res)
+        blocks.append((ttr / (n_instances * train_steps), tev / max(1, n_instances * eval_steps)))
+    return dict(blocks=blocks, per_train_step_s=float(np.median([b[0] for b in blocks])),
+                per_eval_step_s=float(np.median([b[1] for b in blocks])), wall_s=wall, cores=n_jobs,
+                n_instances=n_instances, train_steps=train_steps, eval_steps=eval_steps, repeats=repeats,
+                warmup_steps=warmup_steps)

@@ -32,7 +32,7 @@ def test_pairwise_fixtures(engine, pol):
     assert relerr(r["scores"][0, 0], z["c_scores"]) < 2 * TOL
 
 
-@pytest.mark.parametrize("pol", [0, 3])
+@pytest.mark.parametrize("pol", [0, 1, 3])
 @pytest.mark.parametrize("name,conf", [("graph", False), ("confounders", True)])
 def test_graph_fixtures(engine, name, conf, pol):
     import cgnn_b200.utils.Graph as my_graph

@@ -54,7 +54,7 @@ def _oracle_steps(data, plan, noise, theta0, h):
     return {k: np.array(v) for k, v in out.items()}
 
 
-@pytest.mark.parametrize("pol", [0, 3])
+@pytest.mark.parametrize("pol", [0, 1, 3])          # 1 is what the graph path runs by default (CGNN_EXP_POLICY_GRAPH)
 @pytest.mark.parametrize("n,n_var,h,conf", [(100, 5, 8, False), (257, 11, 20, False), (64, 22, 20, False),
                                             (33, 3, 32, False), (96, 8, 12, True), (130, 19, 20, True), (1, 2, 4, False)])
 def test_graph_step_debug_matches_oracle(engine, n, n_var, h, conf, pol):
@@ -84,8 +84,9 @@ def test_graph_step_debug_matches_oracle(engine, n, n_var, h, conf, pol):
         assert relerr(got["params"][s], ref["params"][s]) < 1e-4
 
 
+@pytest.mark.parametrize("pol", [-1, 3])            # -1: the per-path default
 @pytest.mark.parametrize("n,n_var,h", [(500, 22, 20), (1500, 20, 20)])
-def test_graph_full_size_step(engine, n, n_var, h):
+def test_graph_full_size_step(engine, n, n_var, h, pol):
     """The shapes of the bundled graph example (500 rows, 22 variables, h = 20: both matrices in shared memory) and
     of BASELINE configs[4] (1500 rows, 20 variables: the observed matrix streamed through the per-warp ring)."""
     from cgnn_b200.plan import build_plan, n_params
@@ -96,7 +97,7 @@ def test_graph_full_size_step(engine, n, n_var, h):
     rng = np.random.default_rng(1)
     theta0 = (0.05 * rng.normal(size=n_params(plan, h))).astype(np.float32)
     noise = rng.normal(size=(2, plan["n_noise"], n)).astype(np.float32)
-    got = engine.graph_step_debug(data, plan, noise, theta0, h_layer_dim=h, exp_policy=3)
+    got = engine.graph_step_debug(data, plan, noise, theta0, h_layer_dim=h, exp_policy=pol)
     ref = _oracle_steps(data, oc.build_plan(g), noise, theta0, h)
     for s in range(2):
         assert abs(got["loss"][s] - ref["loss"][s]) <= TOL * abs(ref["loss"][s])
@@ -104,7 +105,8 @@ def test_graph_full_size_step(engine, n, n_var, h):
         assert relerr(got["grad"][s], ref["grad"][s]) < TOL
 
 
-def test_run_graph_external_noise_matches_oracle(engine):
+@pytest.mark.parametrize("pol", [0, -1])            # -1: the policy production runs
+def test_run_graph_external_noise_matches_oracle(engine, pol):
     from cgnn_b200.plan import build_plan, n_params
     from oracle import cgnn as oc
     n, n_var, h, tr, te, runs = 90, 6, 10, 20, 5, 2
@@ -117,7 +119,7 @@ def test_run_graph_external_noise_matches_oracle(engine):
     init = (0.05 * rng.normal(size=(n_inst, ld))).astype(np.float32)
     noise = rng.normal(size=(n_inst, tr + te, n_var, n)).astype(np.float32)
     r = engine.run_graph(data, plans, n_runs=runs, noise=noise, init_params=init, want_trace=True, want_params=True,
-                         h_layer_dim=h, train_epochs=tr, test_epochs=te, trace_every=1, exp_policy=0)
+                         h_layer_dim=h, train_epochs=tr, test_epochs=te, trace_every=1, exp_policy=pol)
     for gi, plan in enumerate(plans):
         P = n_params(plan, h)
         for run in range(runs):
@@ -288,7 +290,7 @@ def test_graph_size_limits(engine):
         engine.run_graph(make_data(64, 33, 2), [build_plan(random_dag(33, 2, 8))], n_runs=1)
 
 
-@pytest.mark.parametrize("pol", [0, 3])
+@pytest.mark.parametrize("pol", [0, 1, 3])
 def test_graph_trained_state_parity(engine, pol):
     """After 150 Adam steps the loss has dropped and dLoss/dPred is a small difference of large PT / PP sums:
     the case that stresses the fp32 accumulation scheme (re-anchored on the kernel's own parameters)."""
@@ -306,6 +308,33 @@ def test_graph_trained_state_parity(engine, pol):
     theta0 = (0.05 * rng.normal(size=n_params(plan, h))).astype(np.float32)
     noise = rng.normal(size=(steps, plan["n_noise"], n)).astype(np.float32)
     got = engine.graph_step_debug(data, plan, noise, theta0, h_layer_dim=h, exp_policy=pol)
+    assert got["loss"][-1] < 0.5 * got["loss"][0]
+    th = got["params"][steps - 2].astype(np.float64)
+    r = oc.step_debug(th, data.astype(np.float64), noise[steps - 1].astype(np.float64), oplan, h)
+    assert abs(got["loss"][-1] - r["loss"]) <= TOL * abs(r["loss"]), (got["loss"][-1], r["loss"])
+    assert relerr(got["dldp"][-1], r["dloss_dpred"]) < TOL
+    assert relerr(got["grad"][-1], r["grad"]) < TOL
+
+
+@pytest.mark.parametrize("n,n_var,steps", [(500, 22, 160), (1500, 20, 120)])
+def test_graph_trained_state_at_the_benchmark_shapes(engine, n, n_var, steps):
+    """The same at the shapes BASELINE.json quotes (bundled example: 500 rows x 22 variables, both matrices in
+    shared memory; configs[4]: 1500 rows x 20 variables, observed matrix streamed), default exp policy: after
+    the loss has dropped, ONE fp64 oracle step re-anchored on the kernel's own parameters - loss, dLoss/dPred and
+    the parameter gradient within 1e-5 (Loss.py:12-32 after CGNN.py:116-121 has run `steps` times)."""
+    from cgnn_b200.plan import build_plan, n_params
+    from oracle import cgnn as oc
+    h = 20
+    g = random_dag(n_var, 2, 31)
+    plan = build_plan(g)
+    oplan = oc.build_plan(g)
+    rng = np.random.default_rng(16)
+    th_gen = (0.8 * rng.normal(size=n_params(plan, h))).astype(np.float64)
+    data = oc.generate(th_gen, rng.normal(size=(plan["n_noise"], n)), oplan, h)
+    data = ((data - data.mean(0)) / data.std(0)).astype(np.float32)
+    theta0 = (0.05 * rng.normal(size=n_params(plan, h))).astype(np.float32)
+    noise = rng.normal(size=(steps, plan["n_noise"], n)).astype(np.float32)
+    got = engine.graph_step_debug(data, plan, noise, theta0, h_layer_dim=h)
     assert got["loss"][-1] < 0.5 * got["loss"][0]
     th = got["params"][steps - 2].astype(np.float64)
     r = oc.step_debug(th, data.astype(np.float64), noise[steps - 1].astype(np.float64), oplan, h)

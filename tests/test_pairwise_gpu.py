@@ -137,7 +137,27 @@ def test_trained_state_parity(engine, pol):
     assert got["loss"][-1] < 0.2 * got["loss"][0]
 
 
-def test_run_pairwise_external_noise_matches_oracle(engine):
+def test_trained_state_at_the_headline_shape(engine):
+    """N = 1500, h = 30, the production exp policy (3: far-tile truncation active on most tile pairs): 300
+    kernel steps, then ONE fp64 oracle step re-anchored on the kernel's own parameters.  The loss is a few 1e-3
+    made of cancelling O(1) block sums (Loss.py:12-32 after GNN.py:92-96 has run 300 times)."""
+    from oracle import gnn as og
+    n, h, steps = 1500, 30, 300
+    rng = np.random.default_rng(19)
+    xy = make_pair(n, 4, kind=0)
+    theta0 = (0.05 * rng.normal(size=4 * h + 1)).astype(np.float32)
+    noise = rng.normal(size=(steps, n)).astype(np.float32)
+    got = engine.pairwise_step_debug(xy, noise, theta0, h_layer_dim=h, exp_policy=3)
+    assert got["loss"][-1] < 0.05 * got["loss"][0]
+    th = got["params"][steps - 2].astype(np.float64)
+    r = og.step_debug(th, xy.astype(np.float64), noise[steps - 1].astype(np.float64), h)
+    assert abs(got["loss"][-1] - r["loss"]) <= TOL * abs(r["loss"]), (got["loss"][-1], r["loss"])
+    assert relerr(got["dldy"][-1], r["dloss_dout"]) < TOL
+    assert relerr(got["grad"][-1], r["grad"]) < TOL
+
+
+@pytest.mark.parametrize("pol", [0, -1])            # -1: the policy production runs (3 on this path)
+def test_run_pairwise_external_noise_matches_oracle(engine, pol):
     from oracle import gnn as og
     n, h, tr, te, runs = 120, 12, 25, 6, 2
     rng = np.random.default_rng(21)
@@ -146,7 +166,7 @@ def test_run_pairwise_external_noise_matches_oracle(engine):
     init = (0.05 * rng.normal(size=(n_inst, 4 * h + 1))).astype(np.float32)
     noise = rng.normal(size=(n_inst, tr + te, n)).astype(np.float32)
     r = engine.run_pairwise(xy, n_runs=runs, noise=noise, init_params=init, want_trace=True, want_params=True,
-                            h_layer_dim=h, train_epochs=tr, test_epochs=te, trace_every=1, exp_policy=0)
+                            h_layer_dim=h, train_epochs=tr, test_epochs=te, trace_every=1, exp_policy=pol)
     for p in range(2):
         for run in range(runs):
             for d in range(2):
