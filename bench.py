@@ -8,7 +8,8 @@ ONE launch of the persistent instance kernel.
 
   value  : generator train-steps/s, whole job, inputs already resident in HBM
   e2e    : the same through the public Python API with HOST buffers (H2D + D2H inside)
-  roofline: algorithmic exp/s of the instance kernel vs this chip's measured MUFU peak
+  roofline: executed MUFU / FMA-pipe work per second (per-evaluation counts from the tracked ncu summary of the current
+            kernel) against this chip's measured pipe peaks; the algorithmic 7-exp / flop figures beside it
   cpu_baseline: the fp32 torch-CPU restatement of the reference graph on the host cores
 
   python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference]
@@ -41,6 +42,38 @@ def algorithmic_work(n_inst, n=N_ROWS, train=TRAIN, test=TEST):
     exps = n_inst * (7 * P * (train + test) + 7 * (n * (n + 1) // 2))
     flops = n_inst * (train * f_train + test * f_eval)
     return exps, flops
+
+
+PROFILE_FILES = {"pairwise": "r2_roofline_pairwise.json", "graph_c2": "r2_roofline_graph_c2.json",
+                 "graph_c5": "r2_roofline_graph_c5.json"}
+
+
+def load_profile(which):
+    """The machine-readable ncu summary of the CURRENT kernel (profiles/*.json, written by tools/ncu_summary.py from one
+    `ncu --set full` capture): executed MUFU / FMA-pipe work per kernel evaluation and DRAM bytes.  It carries the hash
+    of the kernel sources it was taken from; a mismatch with the tree is reported as stale."""
+    from cgnn_b200.build import source_hash
+    path = os.path.join(ROOT, "profiles", PROFILE_FILES[which])
+    if not os.path.exists(path):
+        return None
+    with open(path) as f:
+        doc = json.load(f)
+    doc["file"] = "profiles/" + PROFILE_FILES[which]
+    doc["stale"] = doc.get("source_hash") != source_hash("pairwise" if which == "pairwise" else "graph")
+    return doc
+
+
+def executed_roofline(prof, evals_per_s, mufu_peak, fp32_peak):
+    """Hardware view of a launch: what the kernel actually issued per second against the pipes' measured peaks.
+    mufu = executed ex2 per second / MUFU peak; fma_pipe = FMA-pipe lane-slots per second / (FP32 peak / 2 flop per
+    slot), an FP32x2 instruction counting two slots per lane.  Both are <= 1 by construction."""
+    pe = prof["per_eval"]
+    mufu = pe["mufu_lane_ops"] * evals_per_s / mufu_peak
+    fma = pe["fma_pipe_lane_slots"] * evals_per_s / (fp32_peak / 2.0)
+    return {"mufu_frac": mufu, "fma_pipe_frac": fma, "mufu_per_eval": pe["mufu_lane_ops"],
+            "fma_pipe_slots_per_eval": pe["fma_pipe_lane_slots"], "warp_inst_per_warp_eval": pe["warp_inst_x32"],
+            "profile": prof["file"], "profile_stale": bool(prof["stale"]),
+            "ncu_pipe_pct": prof.get("pipe_pct_of_peak")}
 
 
 class ClockSampler:
@@ -139,7 +172,7 @@ def run_reference(args, rank, world):
     }))
 
 
-def graph_leg(eng, pol, train=60, test=30):
+def graph_leg(eng, pol, peaks, train=60, test=30):
     """Secondary numbers (not the headline metric): the graph instance kernel on this rank's GPU.
     C2 = bundled 22-variable example, the start DAG + its 27 acyclic single reversals x 32 runs (one converged
     hill-climbing sweep, 896 instances, N=500); C5 = synthetic 20-variable DAG, N=1500 after subsampling, 16 runs."""
@@ -159,7 +192,7 @@ def graph_leg(eng, pol, train=60, test=30):
                 out.append(t)
         return out[:limit]
 
-    def one(df, graphs, n_runs, subsets, n):
+    def one(tag, df, graphs, n_runs, subsets, n):
         plans = [build_plan(g, columns=list(df.columns)) for g in graphs]
         X = scale(df.values).astype(np.float32)
         kw = dict(h_layer_dim=20, train_epochs=train, test_epochs=test, exp_policy=pol, seed=1)
@@ -169,12 +202,27 @@ def graph_leg(eng, pol, train=60, test=30):
         n_inst, d = len(plans) * n_runs, X.shape[1]
         P = n * n + n * (n - 1) // 2
         flops = n_inst * (train * (n * n * (5 * d + 28) + (n * (n - 1) // 2) * (7 * d + 28)) + test * (3 * d + 14) * P)
+        # kernel evaluations the launch really performs (gradient pass: both orders of the generated block)
+        evals = n_inst * (train * 2 * n * n + test * (n * n + n * (n + 1) // 2) + n * (n + 1) // 2)
+        fp32_peak = max(peaks["ffma"], peaks["ffma2"])
+        ach = flops / (ms * 1e-3)
+        roof = {"bound": "fp32", "achieved": ach / 1e12, "peak": fp32_peak / 1e12, "unit": "TFLOP/s", "frac": ach / fp32_peak,
+                "algorithmic_flops_per_launch": flops, "kernel_evaluations_per_launch": evals, "traffic": None,
+                "note": "achieved = SURVEY 8(d) algorithmic flops (generated-generated block counted once per unordered pair) / "
+                        "kernel time; the kernel evaluates that block for both orders, so frac <= 0.62 (22 vars) / 0.65 (20 vars) "
+                        "even with the FMA pipe 100 % busy - see executed.fma_pipe_frac for the hardware view"}
+        prof = load_profile(tag)
+        if prof and prof.get("per_eval"):
+            roof["executed"] = executed_roofline(prof, evals / (ms * 1e-3), peaks["mufu"], fp32_peak)
+            w = prof["workload"]
+            roof["traffic"] = int(round((prof["dram_bytes_read"] + prof["dram_bytes_write"]) / w["instances"] * n_inst))
         return {"instances": n_inst, "rows": n, "vars": d, "steps": [train, test], "kernel_ms": ms,
-                "train_steps_per_s": n_inst * train / (ms * 1e-3), "algorithmic_tflops": flops / (ms * 1e-3) / 1e12}
+                "train_steps_per_s": n_inst * train / (ms * 1e-3), "algorithmic_tflops": flops / (ms * 1e-3) / 1e12,
+                "cluster_size": eng.last_graph_cluster, "roofline": roof}
 
     df = pd.read_csv(os.path.join(ex, "Example_graph_numdata.csv"))
     dag = DirectedGraph(pd.read_csv(os.path.join(ex, "Example_graph_target.csv")))
-    res = {"C2_bundled_graph_sweep": one(df, cands(dag), 32, None, 500)}
+    res = {"C2_bundled_graph_sweep": one("graph_c2", df, cands(dag), 32, None, 500)}
     X, edges = synth.make_dag_dataset(20, 2000, 3)
     df5 = pd.DataFrame(X, columns=["V%d" % k for k in range(20)])
     g = DirectedGraph()
@@ -182,9 +230,79 @@ def graph_leg(eng, pol, train=60, test=30):
         g.add("V%d" % a, "V%d" % b, 1.0)
     c5 = cands(g, 10)
     subs = np.stack([np.random.default_rng(k).permutation(2000)[:1500] for k in range(len(c5) * 16)]).astype(np.int32)
-    res["C5_synthetic_20var"] = one(df5, c5, 16, subs, 1500)
+    res["C5_synthetic_20var"] = one("graph_c5", df5, c5, 16, subs, 1500)
     res["note"] = "FP32-pipe bound kernel; algorithmic flops per SURVEY 8(d) (PP counted once per unordered pair)"
     return res
+
+
+def hill_climbing_leg(world, barrier, max_over_ranks):
+    """BASELINE configs[4] end to end through the public API, on all ranks: synthetic 20-variable DAG, n=2000 rows (every
+    run subsamples 1500, CGNN.py:183-185), nb_runs=16, h=20, 1000+500 epochs - pairwise orientation of the skeleton
+    (GNN.orient_graph), then CGNN.orient_directed_graph (hill climbing, CGNN.py:198-252) with every batch of candidate
+    graphs sharded over the ranks.  STRONG scaling: the job is the same at every N."""
+    import pandas as pd
+    import cgnn_b200 as cgnn
+    from cgnn_b200 import synth, SETTINGS as S
+    from cgnn_b200.CGNN import hill_climbing
+    keep = {k: getattr(S, k) for k in ("NB_RUNS", "h_layer_dim", "train_epochs", "test_epochs", "exp_policy", "verbose")}
+    S.NB_RUNS, S.h_layer_dim, S.train_epochs, S.test_epochs, S.exp_policy, S.verbose = 16, 20, 1000, 500, -1, False
+    try:
+        X, edges = synth.make_dag_dataset(20, 2000, 3)
+        df = pd.DataFrame(X, columns=["V%d" % k for k in range(20)])
+        truth = {("V%d" % a, "V%d" % b) for a, b in edges}
+        umg = cgnn.UndirectedGraph(pd.DataFrame(sorted(truth), columns=["Node1", "Node2"]))
+        barrier()
+        t0 = time.perf_counter()
+        dag = cgnn.GNN(backend="B200").orient_graph(df, umg)
+        barrier()
+        t1 = time.perf_counter()
+        pw_hits = sum((a, b) in truth for a, b, _ in dag.get_list_edges())
+        res = cgnn.CGNN(backend="B200").orient_directed_graph(df, dag)
+        barrier()
+        t2 = time.perf_counter()
+    finally:
+        for k, v in keep.items():
+            setattr(S, k, v)
+    s_pw, s_hc = max_over_ranks(t1 - t0), max_over_ranks(t2 - t1)
+    batches = list(hill_climbing.last_batches)
+    n_graphs = int(sum(batches))
+    return {"config": "BASELINE configs[4]: synthetic 20-variable DAG, n=2000 -> 1500 rows per run, nb_runs=16, h=20, 1000+500 epochs",
+            "api": "cgnn_b200.GNN.orient_graph + cgnn_b200.CGNN.orient_directed_graph (host DataFrame in, graph out)",
+            "scaling": "strong", "n_gpus": world, "seconds_pairwise_orientation": s_pw, "seconds_hill_climbing": s_hc,
+            "candidate_graphs_scored": n_graphs, "candidate_graphs_per_s": n_graphs / s_hc,
+            "graph_train_steps_per_s": n_graphs * 16 * 1000 / s_hc, "batches": batches,
+            "instances_per_launch_per_rank": [int(-(-b // world) * 16) for b in batches],
+            "edges": len(truth), "edges_correct_after_pairwise": int(pw_hits),
+            "edges_correct_after_hill_climbing": int(sum((a, b) in truth for a, b, _ in res.get_list_edges())),
+            "limits": "a batch is at most one speculation horizon of candidates (two waves of one GPU per rank); with %d ranks a "
+                      "launch holds the instance counts above against 148 SMs per GPU (instances on clusters of 2-4 CTAs when "
+                      "few), and the host replays the search between batches" % world}
+
+
+def full_sweep_leg(world, barrier, max_over_ranks):
+    """BASELINE configs[3] in full - 1000 pairs x 32 runs x 2 directions x (1000 + 500) steps = 64 000 instances -
+    through cgnn_b200.GNN.predict_dataset on all ranks (host DataFrame in, predictions out)."""
+    import pandas as pd
+    import cgnn_b200
+    from cgnn_b200 import synth, SETTINGS as S
+    keep = {k: getattr(S, k) for k in ("NB_RUNS", "h_layer_dim", "train_epochs", "test_epochs", "exp_policy", "verbose")}
+    S.NB_RUNS, S.h_layer_dim, S.train_epochs, S.test_epochs, S.exp_policy, S.verbose = 32, 30, 1000, 500, -1, False
+    xy, labels = synth.make_pairs(0, 1000, N_ROWS)
+    df = pd.DataFrame({"SampleID": ["pair%d" % k for k in range(1000)],
+                       "A": [xy[k, :, 0].astype(np.float64) for k in range(1000)],
+                       "B": [xy[k, :, 1].astype(np.float64) for k in range(1000)]})
+    model = cgnn_b200.GNN(backend="B200")
+    barrier()
+    t0 = time.perf_counter()
+    try:
+        pred = np.array(model.predict_dataset(df))
+    finally:
+        for k, v in keep.items():
+            setattr(S, k, v)
+    barrier()
+    dt = max_over_ranks(time.perf_counter() - t0)
+    return {"seconds": dt, "pairs": 1000, "instances": 64000, "train_steps_per_s": 64000 * 1000 / dt,
+            "pair_scores_per_s": 1000 / dt, "accuracy_vs_generator_labels": float(np.mean(np.sign(pred) == labels))}
 
 
 def workload_config(args, world):
@@ -212,6 +330,9 @@ def main():
     ap.add_argument("--test", type=int, default=TEST)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-graph", action="store_true", help="skip the secondary graph-kernel measurements")
+    ap.add_argument("--no-hill-climbing", action="store_true", help="skip the BASELINE configs[4] end-to-end leg")
+    ap.add_argument("--full-sweep", choices=["auto", "on", "off"], default="auto",
+                    help="BASELINE configs[3] in full (1000 pairs): auto = only with 4 or more GPUs")
     args = ap.parse_args()
     TRAIN, TEST = args.train, args.test
 
@@ -325,26 +446,44 @@ def main():
     d2h = int(n_inst * 4)
 
     # ---- roofline of the instance kernel ---------------------------------------------------
+    # Two views.  "executed" (the frac): what the kernel issued per second - MUFU ex2 and FMA-pipe lane-slots, per-evaluation
+    # counts from the tracked ncu summary of the current kernel - against the pipes' peaks measured live; <= 1.
+    # "algorithmic": SURVEY 8(d)'s 7 exp and 5d+28 / 7d+28 flops per kernel evaluation over the same time; exp policy 3 derives
+    # four to five of the seven kernels by exact power relations instead of ex2, so its exp figure exceeds the MUFU peak.
     exps, flops = algorithmic_work(n_inst, N_ROWS, TRAIN, TEST)
     k_ms = float(np.mean(kernel_ms))
-    mufu_peak = eng.probe_peak("mufu")
-    ffma_peak = eng.probe_peak("ffma")
+    peaks = {"mufu": eng.probe_peak("mufu"), "ffma": eng.probe_peak("ffma"), "ffma2": eng.probe_peak("ffma2")}
+    fp32_peak = max(peaks["ffma"], peaks["ffma2"])
+    evals = exps / 7.0
     ach_exp = exps / (k_ms * 1e-3)
     ach_flop = flops / (k_ms * 1e-3)
-    roof = {"bound": "mufu", "achieved": ach_exp / 1e12, "peak": mufu_peak / 1e12, "unit": "Texp/s",
-            "frac": ach_exp / mufu_peak, "traffic": int(round(569344.0 / 296.0 * n_inst)),
-            "peak_source": "measured live: cgnn_b200_probe_peak (ex2.approx.ftz chains); MEASURED_PEAKS.json has "
-                           "no MUFU/FP32 entry; nominal 148 SM x 16 lanes x 1.965 GHz = 4.65 Texp/s",
-            "fp32": {"achieved_tflops": ach_flop / 1e12, "peak_tflops": ffma_peak / 1e12, "frac": ach_flop / ffma_peak},
-            "kernel_ms_avg": k_ms, "algorithmic_exps_per_launch": exps, "algorithmic_flops_per_launch": flops,
-            "traffic_note": "DRAM bytes per launch, scaled by the instance count from one ncu --set full capture of a 296-instance x 30-step "
-                            "launch of the same kernel (dram__bytes_read 569,344 + dram__bytes_write 0): dram read 0.55 MB, "
-                            "write 0 (profiles/r1_pairwise_pol3_far_ncu_full.txt) - the working set lives in shared memory",
-            "note": "algorithmic count = 7 exp per kernel evaluation (SURVEY 8d); exp_policy p issues 7/5/4/3 MUFU per "
-                    "evaluation for p=0/1/2/3 (the others come from exact power relations between the bandwidths), so "
-                    "frac can exceed 1.0 (policy 3 also drops the gamma=50 exp for tile pairs whose cause "
-                    "ranges are far apart); ncu pipe utilisation of this kernel (profiles/r1_pairwise_pol3_far_ncu_full.txt): "
-                    "XU 76 %, FMA pipe ~77 %, issue slots 63 %"}
+    prof = load_profile("pairwise")
+    roof = {"kernel_ms_avg": k_ms, "kernel_evaluations_per_launch": evals,
+            "peaks": {"mufu_exp_per_s": peaks["mufu"], "ffma_flop_per_s": peaks["ffma"], "ffma2_flop_per_s": peaks["ffma2"],
+                      "source": "measured live by cgnn_b200_probe_peak (ex2.approx.ftz / fma.rn.f32 / fma.rn.f32x2 chains); "
+                                "MEASURED_PEAKS.json has no MUFU/FP32 entry; nominal 148 SM x 16 (128) lanes x 1.965 GHz = "
+                                "4.65 Texp/s (74.4 TFLOP/s)"},
+            "algorithmic": {"exp_per_s": ach_exp, "exp_frac_of_mufu_peak": ach_exp / peaks["mufu"],
+                            "flop_per_s": ach_flop, "flop_frac_of_fp32_peak": ach_flop / fp32_peak,
+                            "exps_per_launch": exps, "flops_per_launch": flops,
+                            "note": "7 exp per kernel evaluation (SURVEY 8d); not an upper bound for this kernel: exp_policy p "
+                                    "issues 7/5/4/3 ex2 per evaluation (2 for far tile pairs at p=3), the rest by multiplication"}}
+    if prof and prof.get("per_eval"):
+        ex = executed_roofline(prof, evals / (k_ms * 1e-3), peaks["mufu"], fp32_peak)
+        w = prof["workload"]
+        mufu_bound = ex["mufu_frac"] >= ex["fma_pipe_frac"]
+        roof.update({"bound": "mufu" if mufu_bound else "fp32",
+                     "achieved": (ex["mufu_per_eval"] * evals / (k_ms * 1e-3) / 1e12) if mufu_bound
+                                 else (2.0 * ex["fma_pipe_slots_per_eval"] * evals / (k_ms * 1e-3) / 1e12),
+                     "peak": (peaks["mufu"] if mufu_bound else fp32_peak) / 1e12,
+                     "unit": "Texp/s executed" if mufu_bound else "TFLOP/s-equivalent of FMA-pipe slots",
+                     "frac": max(ex["mufu_frac"], ex["fma_pipe_frac"]), "executed": ex,
+                     "traffic": int(round((prof["dram_bytes_read"] + prof["dram_bytes_write"]) / w["instances"] * n_inst)),
+                     "traffic_note": "dram__bytes_read + dram__bytes_write of the profiled launch (%d instances), scaled to this "
+                                     "launch's instance count; the working set lives in shared memory" % w["instances"]})
+    else:       # no tracked profile of this kernel: only the algorithmic FP32 fraction can be stated
+        roof.update({"bound": "fp32", "achieved": ach_flop / 1e12, "peak": fp32_peak / 1e12, "unit": "TFLOP/s",
+                     "frac": ach_flop / fp32_peak, "traffic": None, "executed": None})
 
     out = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
            "warmup": args.warmup, "ms_per_step": dev_ms / args.steps, "higher_is_better": True, "scaling": "weak",
@@ -354,8 +493,18 @@ def main():
                    "pair_scores_per_s": world * args.pairs * args.steps / e2e_s,
                    "api": "cgnn_b200.GNN.predict_dataset(DataFrame of numpy pairs)"},
            "gpu_launches": launches, "clocks": clocks, "roofline": roof}
+    # ---- secondary legs (not the headline metric) -----------------------------------------------
+    hc = None if (args.no_graph or args.no_hill_climbing) else hill_climbing_leg(world, barrier, max_over_ranks)    # all ranks
+    sweep = None
+    if args.full_sweep == "on" or (args.full_sweep == "auto" and world >= 4):
+        sweep = full_sweep_leg(world, barrier, max_over_ranks)                                                         # all ranks
     if not args.no_graph and rank == 0:
-        out["graph_configs"] = graph_leg(eng, args.exp_policy)          # secondary: BASELINE configs[1] / [4] shapes
+        out["graph_configs"] = graph_leg(eng, args.exp_policy, peaks)   # kernel alone: BASELINE configs[1] / [4] shapes, this GPU
+        if hc is not None:
+            out["graph_configs"]["C5_hill_climbing"] = hc
+    if sweep is not None and rank == 0:
+        out["sweep_1000_pairs_s"] = sweep["seconds"]
+        out["sweep_1000_pairs"] = sweep
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         v, r, sample = cpu_baseline_sample(3, 2, 3)
         out["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": r["cores"], "kind": "port", "sample": sample}

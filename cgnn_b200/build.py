@@ -40,6 +40,18 @@ def _deps_mtime():
     return max(os.path.getmtime(d) for d in deps if os.path.exists(d))
 
 
+def source_hash(kind):
+    """Hash of the CUDA sources a kernel family is compiled from ('pairwise' | 'graph').  profiles/*.json written by
+    tools/ncu_summary.py carry it, bench.py recomputes it: a profile of an older kernel is flagged, not trusted."""
+    import hashlib
+    files = {"pairwise": ("common.cuh", "pairwise.cuh"), "graph": ("common.cuh", "graph.cuh")}[kind]
+    h = hashlib.sha256()
+    for f in files:
+        with open(os.path.join(CSRC, f), "rb") as fh:
+            h.update(fh.read())
+    return h.hexdigest()[:16]
+
+
 def build_library(force=False, verbose=False):
     """Compile the CUDA sources into cgnn_b200/libcgnn_b200.so; returns its path."""
     if not force and os.path.exists(LIB) and os.path.getmtime(LIB) >= _deps_mtime():

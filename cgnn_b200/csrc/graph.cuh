@@ -36,6 +36,14 @@ namespace cgnn {
 
 namespace cg = cooperative_groups;
 
+#define GR_PRAGMA(x) _Pragma(#x)
+#define GR_UNROLL(n) GR_PRAGMA(unroll n)
+#ifdef CGNN_GRAD_UNROLL
+#define GR_GRAD_UNROLL GR_UNROLL(CGNN_GRAD_UNROLL)
+#else
+#define GR_GRAD_UNROLL
+#endif
+
 constexpr int GR_NT = 512;
 constexpr int GR_MAX_CLUSTER = 8;
 constexpr int GR_NW = GR_NT / 32;
@@ -293,6 +301,7 @@ __device__ __forceinline__ void gr_mmd_grad_row(const float* __restrict__ Pm, co
         asm volatile("cp.async.wait_group 0;" ::: "memory");
         __syncwarp();
     } else {
+        GR_GRAD_UNROLL
         for (int j = 0; j < N; ++j) gr_grad_pair<DP, POL, TM == GR_T_GMEM>(np, T + size_t(j) * DP, Pm + size_t(j) * DP, acc);
     }
 }

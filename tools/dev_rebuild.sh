@@ -1,0 +1,16 @@
+#!/bin/bash
+# Developer shortcut: recompile only the listed graph-kernel variants (e.g. "22:20 20:20") plus the two API units,
+# relink with the other (cached) objects.  build.py's build_library(force=True) is the real build.
+set -e
+cd "$(dirname "$0")/../cgnn_b200"
+FLAGS="-gencode arch=compute_100a,code=sm_100a -lineinfo -O3 -std=c++17 -Xcompiler -fPIC"
+pids=()
+for v in "$@"; do
+  dp=${v%%:*}; hp=${v##*:}
+  nvcc $FLAGS -DCGNN_DP=$dp -DCGNN_HP=$hp $EXTRA -c csrc/graph_inst.cu -o build/graph_dp${dp}_hp${hp}.o & pids+=($!)
+done
+nvcc $FLAGS -c csrc/capi.cu -o build/capi.o & pids+=($!)
+nvcc $FLAGS -c csrc/graph_api.cu -o build/graph_api.o & pids+=($!)
+for p in "${pids[@]}"; do wait $p; done
+nvcc -shared -o libcgnn_b200.so build/*.o
+echo relinked

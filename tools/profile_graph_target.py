@@ -1,6 +1,8 @@
 """Small fixed workload for ncu: one launch of the graph instance kernel on the bundled 22-variable
 example (148 instances = one wave), or with shape=c5 on the synthetic 20-variable, 1500-row shape of
-BASELINE configs[5].  Usage: python tools/profile_graph_target.py [pol] [train] [test] [c2|c5]"""
+BASELINE configs[4].  Writes gpurun_out/prof_meta_graph_<shape>.json for tools/ncu_summary.py --meta.
+Usage: python tools/profile_graph_target.py [pol] [train] [test] [c2|c5]"""
+import json
 import os, sys
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import numpy as np, pandas as pd
@@ -28,3 +30,13 @@ eng = Engine(0)
 for rep in range(2):
     r = eng.run_graph(X, [plan] * 4, n_runs=37, h_layer_dim=20, train_epochs=train, test_epochs=test, exp_policy=pol, seed=1)
     print("graph pol %d: 148 instances x (%d+%d) steps: kernel %.3f ms, mean score %.4f" % (pol, train, test, eng.last_kernel_ms, float(np.mean(r["scores"]))))
+from cgnn_b200.build import source_hash
+n, d = X.shape
+# kernel evaluations the launch performs: gradient pass N^2 observed + N^2 generated columns per row sweep; loss pass
+# N^2 + N(N+1)/2 (generated block taken once per unordered tile pair); the observed-observed block once per instance
+evals = 148 * (train * 2 * n * n + test * (n * n + n * (n + 1) // 2) + n * (n + 1) // 2)
+flops = 148 * (train * (n * n * (5 * d + 28) + (n * (n - 1) // 2) * (7 * d + 28)) + test * (3 * d + 14) * (n * n + n * (n - 1) // 2))
+meta = dict(family="graph", shape=shape, exp_policy=pol, instances=148, rows=n, vars=d, h=20, train=train, test=test,
+            evals_per_launch=evals, algorithmic_flops_per_launch=flops, source_hash=source_hash("graph"))
+os.makedirs("gpurun_out", exist_ok=True)
+json.dump(meta, open("gpurun_out/prof_meta_graph_%s.json" % shape, "w"))
