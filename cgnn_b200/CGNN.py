@@ -37,7 +37,7 @@ def run_CGNN_b200(df_data, graph, idx=0, run=0, **kwargs):
     scorer = GraphScorer(df_data, confounders=False, **dict(kwargs, nb_runs=1))
     scorer._bind(graph)
     from .plan import build_plan
-    plan = build_plan(graph, columns=scorer.columns)
+    plan = build_plan(graph, columns=scorer.columns, canonical=True)
     uid = structure_uid(structure_key(graph)) + int(run)
     runs = scorer.run_scores_single(plan, uid)
     return float(runs)
@@ -145,7 +145,7 @@ class CGNN(GraphModel):
         from .plan import build_plan, n_params
         data = DataFrame(scale(data.values), columns=data.columns)
         cols = [c for c in data.columns if c in set(dag.get_list_nodes())]
-        plan = build_plan(dag, columns=cols)
+        plan = build_plan(dag, columns=cols, canonical=True)
         X = np.ascontiguousarray(data[cols].values, np.float32)
         eng = runtime.get_engines()[0]
         uid = structure_uid(structure_key(dag)) + int(run)

@@ -24,7 +24,7 @@ def run_CGNN_confounders_b200(df_data, graph, idx=0, run=0, **kwargs):
     scorer = GraphScorer(df_data, confounders=True, **dict(kwargs, nb_runs=1))
     scorer._bind(graph)
     from .plan import build_plan
-    plan = build_plan(graph, columns=scorer.columns, confounders=True)
+    plan = build_plan(graph, columns=scorer.columns, confounders=True, canonical=True)
     return float(scorer.run_scores_single(plan, structure_uid(structure_key(graph)) + int(run)))
 
 

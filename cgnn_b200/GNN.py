@@ -19,13 +19,14 @@ from .utils.Settings import SETTINGS
 _BACKENDS = ("B200", "TensorFlow", "PyTorch")     # the reference's names are aliases of the only engine
 
 
-def _subsample_runs(m, n_runs, uid):
+def _subsample_runs(m, n_runs, uid, run0=0):
     """GNN.py:150-153: a pair longer than SETTINGS.max_nb_points is cut to that many random rows, once
-    per run (both directions of a run share the rows).  Returns [n_runs, max, 2]."""
+    per run (both directions of a run share the rows).  The rows are a function of (seed, pair index, run), so
+    the per-instance seam and the batched path draw the same ones.  Returns [n_runs, max, 2]."""
     cap = int(SETTINGS.max_nb_points)
     out = np.empty((n_runs, cap, 2), np.float32)
     for r in range(n_runs):
-        rng = np.random.default_rng([int(SETTINGS.seed), int(uid), r, 0x5AB5])
+        rng = np.random.default_rng([int(SETTINGS.seed), int(uid), run0 + r, 0x5AB5])
         out[r] = m[rng.permutation(m.shape[0])[:cap]]
     return out
 
@@ -48,12 +49,13 @@ def score_pairs(pairs, idx0=0, **kwargs):
     for every pair (GNN.py:193-194)."""
     nb_runs = int(kwargs.get("nb_runs", SETTINGS.NB_RUNS))
     cap = int(SETTINGS.max_nb_points)
+    sub_idx0, sub_run0 = kwargs.pop("_subsample_key", (idx0, 0))      # (pair index, first run) of the row-subset streams
     mats = [np.ascontiguousarray(m, np.float32) for m in pairs]
     long_pairs = any(m.shape[0] > cap for m in mats)
     if long_pairs:      # one engine "pair" per (pair, run) because every run owns its row subset
         slots = []
         for k, m in enumerate(mats):
-            slots += list(_subsample_runs(m, nb_runs, idx0 + k)) if m.shape[0] > cap else [m] * nb_runs
+            slots += list(_subsample_runs(m, nb_runs, sub_idx0 + k, sub_run0)) if m.shape[0] > cap else [m] * nb_runs
         runs_per_slot = 1
     else:
         slots, runs_per_slot = mats, nb_runs
@@ -79,7 +81,8 @@ def b200_run_instance(m, idx, run, **kwargs):
     """Drop-in for `tf_run_instance(m, idx, run, **kwargs)` (GNN.py:135-166): `[score A->B, score B->A]`
     of ONE run of one pair.  Provided for API parity; prefer the batched calls."""
     nb_runs = int(kwargs.get("nb_runs", SETTINGS.NB_RUNS))
-    kw = dict(kwargs, nb_runs=1, uid_base=int(kwargs.get("uid_base", 0)) + (idx * nb_runs + run) * 2)
+    kw = dict(kwargs, nb_runs=1, uid_base=int(kwargs.get("uid_base", 0)) + (idx * nb_runs + run) * 2,
+              _subsample_key=(idx, run))            # a fresh row subset per (pair, run), as GNN.py:150-153
     s = score_pairs([m], 0, **kw)
     return [float(s[0, 0, 0]), float(s[0, 0, 1])]
 

@@ -11,7 +11,7 @@ class Hparams(C.Structure):
     _fields_ = [("h_layer_dim", C.c_int), ("train_epochs", C.c_int), ("test_epochs", C.c_int),
                 ("learning_rate", C.c_float), ("init_std", C.c_float), ("exp_policy", C.c_int),
                 ("trace_every", C.c_int), ("fast_mmd_vectors", C.c_int), ("seed", C.c_ulonglong),
-                ("graph_cluster", C.c_int), ("reserved1", C.c_int)]
+                ("graph_cluster", C.c_int), ("graph_noise_regen", C.c_int)]
 
 
 class GraphBatchStruct(C.Structure):
@@ -35,6 +35,7 @@ SYMBOLS = {
     "cgnn_b200_last_launch_count": (C.c_int, [_V]),
     "cgnn_b200_device_info": (C.c_int, [_V, _I, _I]),
     "cgnn_b200_last_graph_cluster": (C.c_int, [_V]),
+    "cgnn_b200_last_graph_mode": (C.c_int, [_V]),
     "cgnn_b200_run_pairwise": (C.c_int, [_V, C.POINTER(Hparams), _V, _V, C.c_int, C.c_int, C.c_int,
                                          C.c_ulonglong, _V, _V, _V, _V, _V]),
     "cgnn_b200_pairwise_step_debug": (C.c_int, [_V, C.POINTER(Hparams), _V, C.c_int, C.c_int, _V, _V, _V,

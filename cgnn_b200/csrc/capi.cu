@@ -381,9 +381,23 @@ static int na_fail(char* buf, int len, int code, const char* fmt, ...) {
         if (e_ != cudaSuccess) return na_fail(errbuf, errbuf_len, CGNN_ERR_CUDA, "%s: %s", #call, cudaGetErrorString(e_)); \
     } while (0)
 
+static int noalloc_impl(int device, void* stream, const cgnn_hparams* hp, const float* d_xy, int n_pairs, int n_rows,
+                        int n_runs, unsigned long long uid_base, float* d_scores, char* errbuf, int errbuf_len);
+
 extern "C" int cgnn_b200_run_pairwise_noalloc(int device, void* stream, const cgnn_hparams* hp, const float* d_xy,
                                                int n_pairs, int n_rows, int n_runs, unsigned long long uid_base,
                                                float* d_scores, char* errbuf, int errbuf_len) {
+    // the call makes `device` current for its own work and hands the thread back with the device it came with
+    int prev = -1;
+    const bool have_prev = cudaGetDevice(&prev) == cudaSuccess;
+    if (!have_prev) cudaGetLastError();
+    const int rc = noalloc_impl(device, stream, hp, d_xy, n_pairs, n_rows, n_runs, uid_base, d_scores, errbuf, errbuf_len);
+    if (have_prev && prev != device) cudaSetDevice(prev);
+    return rc;
+}
+
+static int noalloc_impl(int device, void* stream, const cgnn_hparams* hp, const float* d_xy, int n_pairs, int n_rows,
+                        int n_runs, unsigned long long uid_base, float* d_scores, char* errbuf, int errbuf_len) {
     if (errbuf && errbuf_len > 0) errbuf[0] = 0;
     if (!hp || !d_xy || !d_scores) return na_fail(errbuf, errbuf_len, CGNN_ERR_ARG, "hparams, d_xy and d_scores must not be NULL");
     if (hp->h_layer_dim < 1 || hp->h_layer_dim > CGNN_MAX_H)

@@ -26,6 +26,7 @@ struct cgnn_ctx {
     int last_launches = 0;
     int pw_ctas_per_sm = 0;
     int last_cluster = 1;                            // CTAs per instance of the last graph launch
+    int last_graph_mode = 0;                         // shared-memory plan of the last graph launch (cgnn_b200_last_graph_mode)
     // staging buffers (grow-only)
     DevBuf xy, nrows, inst, scores, noise, init, trace, pout, counter, dbg[5];
     DevBuf gT, gdesc, gtidx, gsub, gdata, guid;      // graph path

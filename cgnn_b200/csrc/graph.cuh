@@ -95,6 +95,9 @@ struct GraphArgs {
     // random-feature ("Fourier") MMD, Loss.py:35-56: fast_k = nb_vectors_approx_MMD, 0 = Gaussian-kernel MMD
     int t_smem;                // 1: the observed matrix of the instance is copied to shared memory (it fits)
     int t_ring;                // 1: it does not fit and is streamed through the warps' idle noise buffers (GR_T_RING)
+    int noise_regen;           // 1: noise values are re-derived from their Philox counter at every use instead of being
+                               //    buffered per row block (wide hidden-variable models at 1500 rows: the buffer would not fit)
+    int nbuf_cols;             // floats per lane of a warp's buffer: padded noise columns, or just the ring (DP), or 0
     int fast_k;
     const float* wz_ext;       // NULL or [n_inst][epochs][n_var+1][7*fast_k]: the matrix of Loss.py:35-37 per step
 };
@@ -106,8 +109,8 @@ struct GrSmem {
     float* Ts;                                                           // copy of the observed matrix [NP][DP] (t_smem)
 };
 
-__host__ __device__ inline size_t gr_smem_bytes(int NP, int DP, int n_noise, int p_max, int fast_k = 0, int t_smem = 0) {
-    const int nn_pad = (n_noise + 3) & ~3;
+__host__ __device__ inline size_t gr_smem_bytes(int NP, int DP, int nbuf_cols, int p_max, int fast_k = 0, int t_smem = 0) {
+    const int nn_pad = nbuf_cols;
     const int pp = (p_max + 3) & ~3;
     size_t b = 0;
     b += size_t(pp) * 8;                          // g64
@@ -123,9 +126,28 @@ __host__ __device__ inline size_t gr_smem_bytes(int NP, int DP, int n_noise, int
     return (b + 15) & ~size_t(15);
 }
 
-// ---- noise of one row block into the warp's buffer -------------------------------------------
+// ---- noise ----------------------------------------------------------------------------------------------
+// Column c of row i at a step is element c & 3 of Philox(i, step, GR_STREAM_NOISE0 + c / 4, uid).  Normally a warp draws
+// all columns of its row block once into its buffer (gr_fill_noise); in regeneration mode nothing is buffered and a
+// value is re-derived (or re-read from the caller's noise) wherever a node consumes it.
+struct GrNoise {
+    const float* nb;           // the warp's buffer [column][32 lanes] (buffered mode)
+    const float* ext;          // caller-supplied noise of the step [column][N], or NULL
+    int regen, i, N, lane;
+    unsigned int step, uid;
+    uint2 key;
+};
+__device__ __forceinline__ float gr_noise_get(const GrNoise& z, int c) {
+    if (!z.regen) return z.nb[c * 32 + z.lane];
+    if (z.ext) return (z.i < z.N) ? z.ext[size_t(c) * z.N + z.i] : 0.f;
+    const float4 n = normal4(philox4x32_10(make_uint4(z.i, z.step, GR_STREAM_NOISE0 + (c >> 2), z.uid), z.key));
+    const int e = c & 3;
+    return e == 0 ? n.x : e == 1 ? n.y : e == 2 ? n.z : n.w;
+}
+
 __device__ __forceinline__ void gr_fill_noise(const GrSmem& s, const GraphArgs& a, float* nb, int i, int lane, int step,
                                               unsigned int uid, uint2 key, const float* noise_step) {
+    if (a.noise_regen) return;
     const int nn = s.desc->n_noise;
     if (noise_step) {
         for (int c = 0; c < nn; ++c) nb[c * 32 + lane] = (i < a.N) ? noise_step[size_t(c) * a.N + i] : 0.f;
@@ -141,7 +163,7 @@ __device__ __forceinline__ void gr_fill_noise(const GrSmem& s, const GraphArgs& 
 
 // hidden pre-activations of node k for this lane's row: z[kk] = b_in[kk] + sum_p u_p W_in[p][kk], as HP/2 pairs
 template <int DP, int HP>
-__device__ __forceinline__ void gr_node_z(const GrSmem& s, const float* nb, int k, int i, int lane, float2 (&z)[HP / 2]) {
+__device__ __forceinline__ void gr_node_z(const GrSmem& s, const GrNoise& nz, int k, int i, float2 (&z)[HP / 2]) {
     const GraphDesc& g = *s.desc;
     const float* th = s.theta + g.pad_off[k];
     const int n_in = g.n_in[k], n_par = g.n_par[k];
@@ -150,7 +172,7 @@ __device__ __forceinline__ void gr_node_z(const GrSmem& s, const float* nb, int 
 #pragma unroll
     for (int q = 0; q < HP / 4; ++q) { const float4 b = b4[q]; z[2 * q] = make_float2(b.x, b.y); z[2 * q + 1] = make_float2(b.z, b.w); }
     for (int p = 0; p < n_in; ++p) {
-        const float2 u = splat2((p < n_par) ? s.Pm[i * DP + idx[p]] : nb[idx[p] * 32 + lane]);
+        const float2 u = splat2((p < n_par) ? s.Pm[i * DP + idx[p]] : gr_noise_get(nz, idx[p]));
         const float4* w4 = reinterpret_cast<const float4*>(th + p * HP);
 #pragma unroll
         for (int q = 0; q < HP / 4; ++q) {
@@ -163,11 +185,11 @@ __device__ __forceinline__ void gr_node_z(const GrSmem& s, const float* nb, int 
 
 // Generator forward of one row block (CGNN.py:63-84), nodes in build order.
 template <int DP, int HP>
-__device__ __forceinline__ void gr_forward_block(const GrSmem& s, const float* nb, int i, int lane) {
+__device__ __forceinline__ void gr_forward_block(const GrSmem& s, const GrNoise& nz, int i) {
     const GraphDesc& g = *s.desc;
     for (int k = 0; k < g.n_var; ++k) {
         float2 z[HP / 2];
-        gr_node_z<DP, HP>(s, nb, k, i, lane, z);
+        gr_node_z<DP, HP>(s, nz, k, i, z);
         const float* w_out = s.theta + g.pad_off[k] + (g.n_in[k] + 1) * HP;
         const float4* w4 = reinterpret_cast<const float4*>(w_out);
         float2 acc = make_float2(w_out[HP], 0.f);                       // b_out
@@ -399,11 +421,11 @@ __device__ __forceinline__ float gr_zget(const float2 (&z)[HP / 2], int kk) {
 // Thread-local backward of one row through all nodes in reverse build order; parameter gradients are
 // reduced over the 32 rows of the block (warp_reduce32) and added to the shared fixed-point accumulators.
 template <int DP, int HP>
-__device__ __forceinline__ void gr_backward_block(const GrSmem& s, const float* nb, int i, int lane, float* gl) {
+__device__ __forceinline__ void gr_backward_block(const GrSmem& s, const GrNoise& nz, int i, int lane, float* gl) {
     const GraphDesc& g = *s.desc;
     for (int k = g.n_var - 1; k >= 0; --k) {
         float2 z[HP / 2];
-        gr_node_z<DP, HP>(s, nb, k, i, lane, z);
+        gr_node_z<DP, HP>(s, nz, k, i, z);
         const int n_in = g.n_in[k], n_par = g.n_par[k];
         const int off = g.pad_off[k];
         const short* idx = g.in_idx + g.in_off[k];
@@ -433,7 +455,7 @@ __device__ __forceinline__ void gr_backward_block(const GrSmem& s, const float* 
         if (has_slot) fx_add(&s.g64[off + n_in * HP + slot], double(r));
         // W_in rows and input gradients
         for (int p = 0; p < n_in; ++p) {
-            const float u = (p < n_par) ? s.Pm[i * DP + idx[p]] : nb[idx[p] * 32 + lane];
+            const float u = (p < n_par) ? s.Pm[i * DP + idx[p]] : gr_noise_get(nz, idx[p]);
 #pragma unroll
             for (int kk = 0; kk < HP; ++kk) v[kk] = u * gr_zget<HP>(z, kk);
             r = warp_reduce_n<HP>(v, lane, slot, has_slot);
@@ -602,7 +624,7 @@ __global__ void __launch_bounds__(GR_NT, 1) graph_kernel(const GraphArgs a) {
     GrSmem s;
     {
         unsigned char* p = smem_raw;
-        s.nn_pad = (a.n_noise + 3) & ~3;
+        s.nn_pad = a.nbuf_cols;
         s.g64 = reinterpret_cast<long long*>(p);   p += size_t(pp) * 8;
         s.red = reinterpret_cast<double*>(p);      p += size_t(GR_NW + 4 + GR_MAX_CLUSTER) * 8;
         s.Pm = reinterpret_cast<float*>(p);        p += size_t(a.NP) * DP * 4;
@@ -705,7 +727,7 @@ __global__ void __launch_bounds__(GR_NT, 1) graph_kernel(const GraphArgs a) {
             for (int rb = warp; rb < NB; rb += GR_NW) {
                 const int i = 32 * rb + lane;
                 gr_fill_noise(s, a, nb, i, lane, it, uid, key, noise_step);
-                gr_forward_block<DP, HP>(s, nb, i, lane);
+                gr_forward_block<DP, HP>(s, GrNoise{nb, noise_step, a.noise_regen, i, N, lane, (unsigned)it, uid, key}, i);
                 __syncwarp();
             }
             __syncthreads();
@@ -764,7 +786,7 @@ __global__ void __launch_bounds__(GR_NT, 1) graph_kernel(const GraphArgs a) {
                     for (int c = 0; c < s.desc->n_var; ++c) a.dbg_dldp[(size_t(it) * N + i) * s.desc->n_var + c] = gl[c];
                 if (has) {
                     if (!noise_kept) gr_fill_noise(s, a, nb, i, lane, it, uid, key, noise_step);
-                    gr_backward_block<DP, HP>(s, nb, i, lane, gl);
+                    gr_backward_block<DP, HP>(s, GrNoise{nb, noise_step, a.noise_regen, i, N, lane, (unsigned)it, uid, key}, i, lane, gl);
                     __syncwarp();
                 }
             } else {
@@ -815,7 +837,7 @@ __global__ void __launch_bounds__(GR_NT, 1) graph_kernel(const GraphArgs a) {
                     if (a.dbg_dldp && i < N)
                         for (int c = 0; c < s.desc->n_var; ++c) a.dbg_dldp[(size_t(it) * N + i) * s.desc->n_var + c] = gl[c];
                     if (!noise_kept) gr_fill_noise(s, a, nb, i, lane, it, uid, key, noise_step);
-                    gr_backward_block<DP, HP>(s, nb, i, lane, gl);
+                    gr_backward_block<DP, HP>(s, GrNoise{nb, noise_step, a.noise_regen, i, N, lane, (unsigned)it, uid, key}, i, lane, gl);
                     __syncwarp();
                 }
             }

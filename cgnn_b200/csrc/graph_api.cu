@@ -8,16 +8,24 @@
 using namespace cgnn;
 
 // Gather rows (optionally a subset) of the row-major data matrix into the padded layout T[NP][DP].
-static __global__ void gather_rows_kernel(const float* __restrict__ data, int n_var, const int* __restrict__ subset,
-                                   int N, int NP, int DP, float* __restrict__ T) {
-    const size_t set = blockIdx.y;
-    const int* sub = subset ? subset + set * N : nullptr;
-    float* dst = T + set * size_t(NP) * DP;
-    for (int q = blockIdx.x * blockDim.x + threadIdx.x; q < NP * DP; q += gridDim.x * blockDim.x) {
-        const int r = q / DP, c = q - r * DP;
-        float v = 0.f;
-        if (r < N && c < n_var) v = data[size_t(sub ? sub[r] : r) * n_var + c];
-        dst[q] = v;
+// Row indices of a subset are the caller's: one outside [0, n_rows_total) is never dereferenced - the element becomes 0
+// and *bad is raised, which the host turns into CGNN_ERR_ARG after the batch.  The sets are walked by a grid-stride loop
+// (gridDim.y is capped at 65535, a batch may hold more instances than that).
+static __global__ void gather_rows_kernel(const float* __restrict__ data, int n_var, int n_rows_total, const int* __restrict__ subset,
+                                   int n_sets, int N, int NP, int DP, float* __restrict__ T, int* __restrict__ bad) {
+    for (size_t set = blockIdx.y; set < size_t(n_sets); set += gridDim.y) {
+        const int* sub = subset ? subset + set * N : nullptr;
+        float* dst = T + set * size_t(NP) * DP;
+        for (int q = blockIdx.x * blockDim.x + threadIdx.x; q < NP * DP; q += gridDim.x * blockDim.x) {
+            const int r = q / DP, c = q - r * DP;
+            float v = 0.f;
+            if (r < N && c < n_var) {
+                const int src = sub ? sub[r] : r;
+                if (src >= 0 && src < n_rows_total) v = data[size_t(src) * n_var + c];
+                else *bad = 1;
+            }
+            dst[q] = v;
+        }
     }
 }
 
@@ -137,10 +145,20 @@ static int run_graph_impl(cgnn_ctx* ctx, const cgnn_hparams* hp, const float* da
         d_sub = static_cast<const int*>(dp);
     }
     if ((rc = ensure(ctx, ctx->gT, sizeof(float) * size_t(n_T) * NP * DP))) return rc;
+    if ((rc = ensure(ctx, ctx->counter, 256))) return rc;
+    int* d_bad = static_cast<int*>(ctx->counter.p) + 48;          // words 0 and 32 are the two queue heads
+    CU(cudaMemsetAsync(ctx->counter.p, 0, 256, ctx->stream));
     {
-        dim3 grid((NP * DP + 255) / 256, n_T);
-        gather_rows_kernel<<<grid, 256, 0, ctx->stream>>>(d_data, n_var, d_sub, n_rows, NP, DP, static_cast<float*>(ctx->gT.p));
+        dim3 grid((NP * DP + 255) / 256, std::min(n_T, 65535));
+        gather_rows_kernel<<<grid, 256, 0, ctx->stream>>>(d_data, n_var, n_rows_total, d_sub, n_T, n_rows, NP, DP,
+                                                           static_cast<float*>(ctx->gT.p), d_bad);
         CU(cudaGetLastError());
+    }
+    if (row_subsets) {       // refuse the batch before the long kernel runs on zero-filled rows
+        int bad = 0;
+        CU(cudaMemcpyAsync(&bad, d_bad, sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
+        CU(cudaStreamSynchronize(ctx->stream));
+        if (bad) return fail(ctx, CGNN_ERR_ARG, "row_subsets holds an index outside [0, n_rows_total=%d)", n_rows_total);
     }
     a.T = static_cast<const float*>(ctx->gT.p);
     if (row_subsets) {
@@ -187,9 +205,7 @@ static int run_graph_impl(cgnn_ctx* ctx, const cgnn_hparams* hp, const float* da
     a.trace = static_cast<float*>(op);
     if ((rc = stage_out(ctx, ctx->pout, params_out, sizeof(float) * size_t(n_inst) * ld_params, &op))) return rc;
     a.params_out = static_cast<float*>(op);
-    if ((rc = ensure(ctx, ctx->counter, 256))) return rc;
-    a.counter = static_cast<int*>(ctx->counter.p);
-    CU(cudaMemsetAsync(a.counter, 0, 256, ctx->stream));
+    a.counter = static_cast<int*>(ctx->counter.p);             // zeroed above, before the gather
 
     size_t dbg_bytes[5] = {0, 0, 0, 0, 0};
     float* dbg_dev[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
@@ -216,15 +232,31 @@ static int run_graph_impl(cgnn_ctx* ctx, const cgnn_hparams* hp, const float* da
     a.lr = hp->learning_rate; a.init_std = hp->init_std; a.ld_params = ld_params;
     a.key = make_uint2((unsigned int)(hp->seed & 0xffffffffu), (unsigned int)(hp->seed >> 32));
 
-    // the observed matrix goes to shared memory too when everything still fits one SM (decided by the instance
-    // shape only; the arithmetic is the same either way)
-    const size_t smem_ts = gr_smem_bytes(NP, DP, n_noise, p_pad_max, a.fast_k, 1);
-    a.t_smem = (a.fast_k == 0 && smem_ts <= size_t(ctx->prop.sharedMemPerBlockOptin)) ? 1 : 0;
-    const size_t smem = a.t_smem ? smem_ts : gr_smem_bytes(NP, DP, n_noise, p_pad_max, a.fast_k);
-    a.t_ring = (!a.t_smem && a.fast_k == 0 && ((n_noise + 3) & ~3) >= DP) ? 1 : 0;
-    if (smem > size_t(ctx->prop.sharedMemPerBlockOptin))
-        return fail(ctx, CGNN_ERR_LIMIT, "graph instance needs %zu B of shared memory (rows %d x cols %d, %d noise columns, %d parameters); "
-                    "device allows %zu", smem, n_rows, DP, n_noise, p_max, size_t(ctx->prop.sharedMemPerBlockOptin));
+    // Shared-memory plan of an instance, fastest first (the arithmetic is the same in all of them; it is decided by
+    // the instance shape only):
+    //   noise buffered per row block + observed matrix in shared memory  >  ... streamed through the warps' noise
+    //   buffers (ring)  >  ... read through L1/L2  >  the same three with the noise re-derived at every use instead of
+    //   buffered (wide hidden-variable models at 1500 rows: 16 warps x all noise columns would not fit).
+    const size_t smem_max = size_t(ctx->prop.sharedMemPerBlockOptin);
+    const int nn_pad = (n_noise + 3) & ~3;
+    size_t smem = 0;
+    bool placed = false;
+    for (int regen = hp->graph_noise_regen ? 1 : 0; regen < 2 && !placed; ++regen)
+        for (int tm = 0; tm < 3 && !placed; ++tm) {              // 0: observed matrix in smem, 1: ring, 2: global
+            if (a.fast_k > 0 && tm != 2) continue;               // random-feature mode reads the observed rows from global
+            const int cols = regen ? (tm == 1 ? DP : 0) : nn_pad;
+            if (tm == 1 && cols < DP) continue;                  // the ring needs 2 x 16 rows of DP floats per warp
+            const size_t need = gr_smem_bytes(NP, DP, cols, p_pad_max, a.fast_k, tm == 0);
+            if (need > smem_max) continue;
+            a.noise_regen = regen; a.nbuf_cols = cols; a.t_smem = tm == 0; a.t_ring = tm == 1;
+            smem = need;
+            placed = true;
+        }
+    if (!placed)
+        return fail(ctx, CGNN_ERR_LIMIT, "graph instance does not fit shared memory (rows %d x cols %d, %d noise columns, %d parameters): "
+                    "even without noise and observed-matrix buffers it needs %zu B, device allows %zu", n_rows, DP, n_noise, p_max,
+                    gr_smem_bytes(NP, DP, 0, p_pad_max, a.fast_k, 0), smem_max);
+    ctx->last_graph_mode = a.noise_regen * 4 + (a.t_smem ? 0 : a.t_ring ? 1 : 2);
     const int pol = hp->exp_policy < 0 ? CGNN_EXP_POLICY_GRAPH : hp->exp_policy;
     // ---- CTAs per instance: a cluster when the batch cannot fill the GPU with one CTA per instance ----------
     const int NB = NP / 32;
@@ -302,6 +334,8 @@ static int run_graph_impl(cgnn_ctx* ctx, const cgnn_hparams* hp, const float* da
 }
 
 extern "C" {
+
+int cgnn_b200_last_graph_mode(const cgnn_ctx* ctx) { return ctx ? ctx->last_graph_mode : -1; }
 
 int cgnn_b200_run_graph(cgnn_ctx* ctx, const cgnn_hparams* hp, const float* data, int n_rows_total,
                         const cgnn_graph_batch* graphs, int n_runs, const int* row_subsets, int n_rows,

@@ -43,6 +43,7 @@ def make_hparams(**kw):
     hp.fast_mmd_vectors = int(kw.get("nb_vectors_approx_MMD", SETTINGS.nb_vectors_approx_MMD)) if fast else 0
     hp.seed = int(kw.get("seed", SETTINGS.seed)) & 0xFFFFFFFFFFFFFFFF
     hp.graph_cluster = int(kw.get("graph_cluster", 0))
+    hp.graph_noise_regen = int(kw.get("graph_noise_regen", 0))
     return hp
 
 
@@ -85,6 +86,12 @@ class Engine:
     @property
     def last_graph_cluster(self):
         return int(self._lib.cgnn_b200_last_graph_cluster(self._h))
+
+    @property
+    def last_graph_mode(self):
+        """Shared-memory plan of the last graph call: (observed matrix: 0 smem / 1 ring / 2 global) + 4 if the noise
+        was regenerated at every use instead of buffered."""
+        return int(self._lib.cgnn_b200_last_graph_mode(self._h))
 
     def device_info(self):
         a, b = C.c_int(), C.c_int()

@@ -17,23 +17,31 @@ import numpy as np
 from . import _lib
 
 
-def build_plan(graph, columns=None, confounders=False):
+def build_plan(graph, columns=None, confounders=False, canonical=False):
+    """canonical=False restates the reference literally: node scan order, parent order and neighbour order are those of
+    the graph object (its insertion history).  canonical=True orders everything by data column instead, so that two graph
+    objects with the same edge set always give the same plan - what the search drivers need, whose cache and random
+    streams are keyed by the edge set alone (the flat parameter layout, hence which initial weight a connection
+    draws, follows the plan's order)."""
     if confounders:
         skel = graph.skeleton
         list_nodes = skel.get_list_nodes()                          # CGNN_confounders.py:57
         skel_edges = skel.get_list_edges_without_duplicate()        # CGNN_confounders.py:64
-        shared = {}
-        for k, (n1, n2) in enumerate(skel_edges):
-            shared[(n1, n2)] = shared[(n2, n1)] = k
     else:
         list_nodes = graph.get_list_nodes()                         # CGNN.py:55
-        skel_edges, shared = [], {}
+        skel_edges = []
     columns = list(columns) if columns is not None else list(list_nodes)
     col = {v: c for c, v in enumerate(columns)}
     n_var = len(list_nodes)
     if sorted(col[v] for v in list_nodes) != list(range(n_var)):
         raise ValueError("graph nodes and data columns do not match")
-    parents = {v: graph.get_parents(v) for v in list_nodes}
+    if canonical:
+        list_nodes = sorted(list_nodes, key=col.get)
+        skel_edges = sorted((tuple(sorted((e[0], e[1]), key=col.get)) for e in skel_edges), key=lambda e: (col[e[0]], col[e[1]]))
+    shared = {}
+    for k, e in enumerate(skel_edges):
+        shared[(e[0], e[1])] = shared[(e[1], e[0])] = k
+    parents = {v: (sorted(graph.get_parents(v), key=col.get) if canonical else graph.get_parents(v)) for v in list_nodes}
     emitted, order = set(), []
     while len(order) < n_var:                                       # CGNN.py:63-69
         before = len(order)
@@ -47,7 +55,8 @@ def build_plan(graph, columns=None, confounders=False):
     for v in order:
         noise = [col[v]]
         if confounders:
-            noise += [n_var + shared[(nb, v)] for nb in graph.skeleton.get_neighbors(v)]
+            nbs = graph.skeleton.get_neighbors(v)
+            noise += [n_var + shared[(nb, v)] for nb in (sorted(nbs, key=col.get) if canonical else nbs)]
         nodes.append(dict(col=col[v], parents=[col[p] for p in parents[v]], noise=noise))
     return dict(n_var=n_var, n_noise=n_var + len(skel_edges), nodes=nodes, list_nodes=list(list_nodes),
                 columns=columns, n_edges=sum(len(nd["parents"]) for nd in nodes))

@@ -16,7 +16,9 @@ MEMOISED RE-EXECUTION:
   4. repeat until a run finishes without a miss; that run's graph is the result.
 
 A candidate's score is a deterministic function of (seed, graph structure): its Philox streams are
-keyed by a hash of the edge set.  So a candidate scored speculatively and then not needed changes
+keyed by a hash of the edge set and its plan is built in canonical (data-column) order, so the same
+edge set reached through a different sequence of moves is the same model with the same initial
+weights.  So a candidate scored speculatively and then not needed changes
 nothing, and the final run takes exactly the decisions a one-by-one evaluation would take:
 first-improvement order, tabu list, strict `<` acceptance are all those of the sequential code.
 """
@@ -113,7 +115,7 @@ class GraphScorer(object):
         """Mean finite run score of every graph: one sharded engine submission."""
         if self.data is None:
             self._bind(graphs[0])
-        plans = [build_plan(g, columns=self.columns, confounders=self.confounders) for g in graphs]
+        plans = [build_plan(g, columns=self.columns, confounders=self.confounders, canonical=True) for g in graphs]
         keys = [structure_key(g) for g in graphs]
         n_total, cap = self.data.shape[0], int(SETTINGS.max_nb_points)
         runs = self.run_scores(plans, keys, n_total, cap)

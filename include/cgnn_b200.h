@@ -76,7 +76,9 @@ typedef struct cgnn_hparams {
     unsigned long long seed;  /* engine Philox seed.  The reference is unseeded (no hit for "seed" in its tree). */
     int   graph_cluster;      /* graph path: CTAs (SMs) per instance, 1..4; 0 = chosen per batch (a thread-block cluster
                                  when the batch has too few instances to fill the GPU otherwise) */
-    int   reserved1;
+    int   graph_noise_regen;  /* graph path: 0 = buffer a row block's noise columns when they fit shared memory (default),
+                                 1 = always re-derive them at every use (the plan the engine falls back to when they do
+                                 not fit; same random streams, bit-identical results - this switch exists for testing) */
 } cgnn_hparams;
 
 /* ---- life cycle ------------------------------------------------------------------------- */
@@ -238,7 +240,10 @@ int  cgnn_b200_graph_step_debug(cgnn_ctx* ctx, const cgnn_hparams* hp,
  *  - The array is shared by every call in the process and keeps the previous call's contents; each
  *    call re-initialises the parts that must start from zero on `stream` before its main launch.
  *    Two calls whose GPU work overlaps (different streams or threads) race on it: serialise them.
- *  - Synchronous like the other entry points: returns after `stream` has drained. */
+ *  - Synchronous like the other entry points, on EVERY call and not only the first: it inspects the two pointers
+ *    (cudaPointerGetAttributes), enqueues its work on `stream` and waits (cudaStreamSynchronize) until `stream`
+ *    has drained before it returns.
+ *  - `device` is made current while the call works; the calling thread gets back the device it had before. */
 int  cgnn_b200_run_pairwise_noalloc(int device, void* stream, const cgnn_hparams* hp,
                                     const float* d_xy, int n_pairs, int n_rows, int n_runs,
                                     unsigned long long uid_base, float* d_scores,
@@ -256,6 +261,12 @@ int  cgnn_b200_device_info(const cgnn_ctx* ctx, int* n_sm, int* ctas_per_sm_pair
 
 /* CTAs per instance (cluster size) the last cgnn_b200_run_graph call on this context used. */
 int  cgnn_b200_last_graph_cluster(const cgnn_ctx* ctx);
+
+/* Shared-memory plan the last graph call used (diagnostic; results do not depend on it): low two bits = where the
+ * observed matrix is read from (0 shared memory, 1 streamed through the warps' buffers, 2 global/L2); +4 = the noise
+ * columns are re-derived from their Philox counters at every use instead of being buffered per row block - the plan
+ * for hidden-variable models (CGNN_confounders.py:66-96: one extra noise column per skeleton edge) at 1500 rows. */
+int  cgnn_b200_last_graph_mode(const cgnn_ctx* ctx);
 
 #ifdef __cplusplus
 }

@@ -341,3 +341,65 @@ def test_graph_trained_state_at_the_benchmark_shapes(engine, n, n_var, steps):
     assert abs(got["loss"][-1] - r["loss"]) <= TOL * abs(r["loss"]), (got["loss"][-1], r["loss"])
     assert relerr(got["dldp"][-1], r["dloss_dpred"]) < TOL
     assert relerr(got["grad"][-1], r["grad"]) < TOL
+
+
+def _wide_confounder_graph(n_var=20, n_skel=30, seed=3):
+    """An oriented 20-variable graph over a 30-edge skeleton (max_nb_points-sized problems of the hidden-variable model)."""
+    import pandas as pd
+    from cgnn_b200.utils.Graph import DirectedGraph, UndirectedGraph
+    rng = np.random.default_rng(seed)
+    pairs = set()
+    for k in range(1, n_var):                                   # a spanning tree first: every variable has a neighbour
+        pairs.add((int(rng.integers(0, k)), k))
+    while len(pairs) < n_skel:
+        a, b = sorted(rng.choice(n_var, 2, replace=False).tolist())
+        pairs.add((a, b))
+    pairs = sorted(pairs)
+    skel = UndirectedGraph(pd.DataFrame([("V%d" % a, "V%d" % b) for a, b in pairs], columns=["Cause", "Effect"]))
+    g = DirectedGraph(skeleton=skel)
+    for a, b in pairs:
+        g.add("V%d" % a, "V%d" % b, float(rng.uniform(0.1, 1)))   # low index -> high index: acyclic
+    return g
+
+
+def test_wide_hidden_variable_model_at_1500_rows(engine):
+    """20 variables, a 30-edge skeleton (50 noise columns), SETTINGS.max_nb_points = 1500 rows: buffering every noise column
+    per row block would need more shared memory than an SM has, so the engine re-derives the noise at every use
+    (CGNN_confounders.py:66-96 at the reference's default size).  One train step against the fp64 oracle, then a short
+    scored batch."""
+    from cgnn_b200.plan import build_plan, n_params
+    from oracle import cgnn as oc
+    n, h = 1500, 20
+    g = _wide_confounder_graph()
+    plan = build_plan(g, confounders=True)
+    oplan = oc.build_plan(g, confounders=True)
+    assert plan["n_noise"] == 50
+    data = make_data(n, 20, 8)
+    rng = np.random.default_rng(2)
+    theta0 = (0.05 * rng.normal(size=n_params(plan, h))).astype(np.float32)
+    noise = rng.normal(size=(1, plan["n_noise"], n)).astype(np.float32)
+    got = engine.graph_step_debug(data, plan, noise, theta0, h_layer_dim=h)
+    assert engine.last_graph_mode & 4, "expected the noise-regeneration plan at this size"
+    ref = _oracle_steps(data, oplan, noise, theta0, h)
+    assert abs(got["loss"][0] - ref["loss"][0]) <= TOL * abs(ref["loss"][0])
+    assert relerr(got["dldp"][0], ref["dldp"][0]) < TOL
+    assert relerr(got["grad"][0], ref["grad"][0]) < TOL
+    r = engine.run_graph(data, [plan], n_runs=3, h_layer_dim=h, train_epochs=6, test_epochs=3, seed=5)
+    assert engine.last_graph_mode & 4
+    assert np.all(np.isfinite(r["scores"])) and np.all(r["scores"] > 0) and len(set(r["scores"].ravel().tolist())) == 3
+
+
+@pytest.mark.parametrize("conf", [False, True])
+def test_noise_regeneration_is_bit_identical(engine, conf):
+    """The same instances with the noise buffered per row block and re-derived at every use (in-kernel Philox streams):
+    identical trained parameters and scores."""
+    from cgnn_b200.plan import build_plan
+    g = random_dag(9, 2, 14, with_skeleton=conf)
+    plan = build_plan(g, confounders=conf)
+    data = make_data(300, 9, 4)
+    kw = dict(n_runs=3, h_layer_dim=12, train_epochs=10, test_epochs=4, seed=21, want_params=True)
+    a = engine.run_graph(data, [plan], **kw)
+    assert not engine.last_graph_mode & 4
+    b = engine.run_graph(data, [plan], graph_noise_regen=1, **kw)
+    assert engine.last_graph_mode & 4
+    assert np.array_equal(a["params"], b["params"]) and np.array_equal(a["scores"], b["scores"])

@@ -163,3 +163,18 @@ def test_orient_graph_matches_reference_flow(conf, capsys):
         assert rg.get_dict_nw() == g.get_dict_nw()
         for (a, b, w), (a2, b2, w2) in zip(rg.get_list_edges(), g.get_list_edges()):
             assert (a, b) == (a2, b2) and abs(w - w2) < 1e-12
+
+
+def test_run_instance_seam_equals_the_batched_path_for_long_pairs(fake):
+    """A pair longer than SETTINGS.max_nb_points is cut to a fresh random row subset per run (GNN.py:150-153).  The
+    per-instance seam (drop-in for tf_run_instance) must draw the subset of ITS (pair, run) - not the same rows for every
+    run - and so reproduce the batched scores."""
+    from cgnn_b200 import SETTINGS
+    from cgnn_b200.GNN import b200_run_instance, score_pairs
+    rng = np.random.default_rng(3)
+    m = rng.normal(size=(1700, 2)).astype(np.float32)
+    assert m.shape[0] > SETTINGS.max_nb_points
+    batched = score_pairs([m], 3, nb_runs=4)
+    single = np.array([b200_run_instance(m, 3, run, nb_runs=4) for run in range(4)], np.float32)
+    assert np.array_equal(batched[0], single)
+    assert len({tuple(r) for r in single.tolist()}) == 4           # four different row subsets

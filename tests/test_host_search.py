@@ -147,3 +147,32 @@ def test_confounder_search_with_a_missing_edge_uses_the_add_branch(quiet, monkey
             with contextlib.redirect_stdout(io.StringIO()):
                 r = ref["CGNN_confounders"].hill_climbing_confounders(g3, data, fake_fn, nb_runs=2, nb_jobs=1)
             assert _edges(r) == _edges(seq)
+
+
+def test_canonical_plan_ignores_insertion_history():
+    """The search caches scores by edge set; the plan (hence the flat parameter layout and which initial weight each
+    connection draws) must then be a function of the edge set alone - not of the order in which edges were added or
+    reversed."""
+    import pandas as pd
+    from cgnn_b200.plan import build_plan
+    from cgnn_b200.utils.Graph import DirectedGraph, UndirectedGraph
+    edges = [("V3", "V1"), ("V0", "V1"), ("V1", "V2"), ("V0", "V4"), ("V4", "V2")]
+    cols = ["V%d" % k for k in range(5)]
+    skel = UndirectedGraph(pd.DataFrame(edges, columns=["Cause", "Effect"]))
+    skel2 = UndirectedGraph(pd.DataFrame([(b, a) for a, b in reversed(edges)], columns=["Cause", "Effect"]))
+    plans = []
+    for order, sk in ((edges, skel), (list(reversed(edges)), skel2)):
+        g = DirectedGraph(skeleton=sk)
+        for a, b in order:
+            g.add(a, b, 1.0)
+        g.reverse_edge("V0", "V4"); g.reverse_edge("V4", "V0")          # same edge set again, different insertion history
+        plans.append((build_plan(g, columns=cols, canonical=True), build_plan(g, columns=cols, confounders=True, canonical=True)))
+    for a, b in zip(plans[0], plans[1]):
+        assert a["nodes"] == b["nodes"] and a["n_noise"] == b["n_noise"]
+    # the literal (reference-order) plans do differ - that is what canonical=True removes
+    g1, g2 = DirectedGraph(), DirectedGraph()
+    for a, b in edges:
+        g1.add(a, b, 1.0)
+    for a, b in reversed(edges):
+        g2.add(a, b, 1.0)
+    assert build_plan(g1, columns=cols)["nodes"] != build_plan(g2, columns=cols)["nodes"]

@@ -47,3 +47,26 @@ def test_noalloc_matches_run_pairwise_twice(engine):
     # host memory is refused (staging it would need an allocation)
     with pytest.raises(ValueError):
         run_pairwise_noalloc(torch.zeros((1, 64, 2)), out[:, :1], n_runs=1)
+
+
+def test_noalloc_c_level_refusals(engine):
+    """Straight through ctypes, past the Python wrapper's own checks: host pointers are refused with CGNN_ERR_ARG and a
+    message (staging them would need the allocation this entry point exists to avoid), and the calling thread keeps
+    its current device."""
+    import ctypes as C
+    import torch
+    from cgnn_b200 import _lib
+    from cgnn_b200.engine import make_hparams
+    lib = _lib.load()
+    hp = make_hparams(h_layer_dim=8, train_epochs=1, test_epochs=1)
+    host_xy = np.zeros((1, 64, 2), np.float32)
+    d_sc = torch.zeros((1, 1, 2), dtype=torch.float32, device="cuda")
+    err = C.create_string_buffer(256)
+    dev_before = torch.cuda.current_device()
+    rc = lib.cgnn_b200_run_pairwise_noalloc(0, C.c_void_p(0), C.byref(hp), C.c_void_p(host_xy.ctypes.data), 1, 64, 1,
+                                            C.c_ulonglong(0), C.c_void_p(d_sc.data_ptr()), err, len(err))
+    assert rc == -1 and b"device memory" in err.value                     # CGNN_ERR_ARG
+    rc = lib.cgnn_b200_run_pairwise_noalloc(0, C.c_void_p(0), C.byref(hp), None, 1, 64, 1, C.c_ulonglong(0),
+                                            C.c_void_p(d_sc.data_ptr()), err, len(err))
+    assert rc == -1 and b"NULL" in err.value
+    assert torch.cuda.current_device() == dev_before

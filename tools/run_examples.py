@@ -1,5 +1,5 @@
 """Runs the three bundled examples (BASELINE configs[0..2]) at the reference's own settings through the
-public API and scores the decisions against the bundled ground truth.  Writes profiles/r1_examples_full.json.
+public API and scores the decisions against the bundled ground truth.  Writes profiles/r2_examples_full.json.
 Usage: python tools/run_examples.py [--runs 32] [--train 1000] [--test 500] [--seeds 1]"""
 import argparse, json, os, sys, time
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
@@ -17,7 +17,7 @@ ap.add_argument("--runs", type=int, default=32)
 ap.add_argument("--train", type=int, default=1000)
 ap.add_argument("--test", type=int, default=500)
 ap.add_argument("--seeds", type=int, default=1)
-ap.add_argument("--out", default="profiles/r1_examples_full.json")
+ap.add_argument("--out", default="profiles/r2_examples_full.json")
 a = ap.parse_args()
 EX = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "examples")
 S = cgnn.SETTINGS
@@ -74,7 +74,15 @@ for seed in range(a.seeds):
     out = cgnn.CGNN_confounders(backend="TensorFlow").orient_directed_graph(df, dag)
     found = {(x, y) for x, y, _ in out.get_list_edges()}
     spurious = {frozenset(e) for e in (("V11", "V9"), ("V12", "V14"), ("V17", "V19"))}
+    # a kept edge's weight is what its removal would cost: score(without the edge) - score(with it), penalty included
+    # (CGNN_confounders.py:314-317) - so the weights of the three spurious links say why they stay
+    wts = {(x, y): float(w) for x, y, w in out.get_list_edges()}
+    sp_cost = {"%s-%s" % tuple(sorted(e)): [w for (x, y), w in wts.items() if frozenset((x, y)) == e] for e in spurious}
+    true_cost = sorted(w for e, w in wts.items() if e in truth)
     r["confounders"] = dict(n_edges=len(found), true_positive=len(found & truth), n_truth=len(truth),
+                            removal_cost_of_spurious_links=sp_cost,
+                            removal_cost_of_true_edges_min_median_max=[true_cost[0], true_cost[len(true_cost) // 2], true_cost[-1]] if true_cost else None,
+                            complexity_penalty_per_edge=float(S.complexity_graph_param),
                             spurious_links_removed=int(sum(frozenset(e) not in {frozenset(f) for f in found} for e in spurious)),
                             acyclic=not out.is_cyclic(), batches=list(hill_climbing_confounders.last_batches),
                             seconds_pairwise=t1 - t0, seconds_cgnn=time.time() - t1)
