@@ -279,6 +279,49 @@ def hill_climbing_leg(world, barrier, max_over_ranks):
                       "few), and the host replays the search between batches" % world}
 
 
+def ragged_leg(world, barrier, max_over_ranks, n_pairs_per_rank=40):
+    """Pairs of different lengths (300 ... 1500 rows, cost ~ rows^2) over the ranks: static equal shards against the
+    chunked work-stealing schedule of cgnn_b200/runtime.py (SETTINGS.work_stealing; the reference places run r on
+    GPU r % nb_gpu, GNN.py:158-163).  Same pairs, same scores; reports the two wall times and who took which chunks."""
+    import cgnn_b200
+    from cgnn_b200 import synth, runtime, SETTINGS as S
+    from cgnn_b200.GNN import score_pairs
+    keep = {k: getattr(S, k) for k in ("work_stealing", "verbose")}
+    S.verbose = False
+    n_pairs = n_pairs_per_rank * world
+    lens = [300 + (1200 * ((7 * k) % n_pairs)) // max(1, n_pairs - 1) for k in range(n_pairs)]
+    lens.sort(reverse=True)                                   # worst case for contiguous static shards: rank 0 gets the long ones
+    pairs = [synth.make_pair(50000 + k, n)[0] for k, n in enumerate(lens)]
+    kw = dict(nb_runs=8, h_layer_dim=H, train_epochs=200, test_epochs=100, seed=0)
+    out = {}
+    try:
+        for name, steal in (("static", False), ("work_stealing", True)):
+            S.work_stealing = steal
+            real = runtime.run_batch
+
+            def forced(n_items, items_per_uid, uid_base, call, tail_shape=(), costs=None):   # static: ignore the cost hint
+                return real(n_items, items_per_uid, uid_base, call, tail_shape, costs if steal else None)
+            runtime.run_batch = forced                           # cgnn_b200.GNN calls runtime.run_batch through the module
+            try:
+                score_pairs(pairs[:world], 0, **kw)               # warm-up
+                barrier()
+                t0 = time.perf_counter()
+                sc = score_pairs(pairs, 0, **kw)
+                barrier()
+                out[name] = {"seconds": max_over_ranks(time.perf_counter() - t0), "checksum": float(np.sum(sc.astype(np.float64)))}
+                if steal:
+                    out[name]["chunks_taken_by_rank0"] = list(getattr(runtime.run_stolen, "last_owned", []))
+            finally:
+                runtime.run_batch = real
+    finally:
+        for k, v in keep.items():
+            setattr(S, k, v)
+    out["same_scores"] = out["static"]["checksum"] == out["work_stealing"]["checksum"]
+    out["rows"] = [min(lens), max(lens)]
+    out["pairs"] = n_pairs
+    return out
+
+
 def full_sweep_leg(world, barrier, max_over_ranks):
     """BASELINE configs[3] in full - 1000 pairs x 32 runs x 2 directions x (1000 + 500) steps = 64 000 instances -
     through cgnn_b200.GNN.predict_dataset on all ranks (host DataFrame in, predictions out)."""
@@ -495,6 +538,7 @@ def main():
            "gpu_launches": launches, "clocks": clocks, "roofline": roof}
     # ---- secondary legs (not the headline metric) -----------------------------------------------
     hc = None if (args.no_graph or args.no_hill_climbing) else hill_climbing_leg(world, barrier, max_over_ranks)    # all ranks
+    ragged = ragged_leg(world, barrier, max_over_ranks) if (world > 1 and not args.no_graph) else None                 # all ranks
     sweep = None
     if args.full_sweep == "on" or (args.full_sweep == "auto" and world >= 4):
         sweep = full_sweep_leg(world, barrier, max_over_ranks)                                                         # all ranks
@@ -502,6 +546,8 @@ def main():
         out["graph_configs"] = graph_leg(eng, args.exp_policy, peaks)   # kernel alone: BASELINE configs[1] / [4] shapes, this GPU
         if hc is not None:
             out["graph_configs"]["C5_hill_climbing"] = hc
+    if ragged is not None and rank == 0:
+        out["ragged_pairs_work_stealing"] = ragged
     if sweep is not None and rank == 0:
         out["sweep_1000_pairs_s"] = sweep["seconds"]
         out["sweep_1000_pairs"] = sweep
