@@ -2,7 +2,8 @@
 
 The shared library is the product; it is built here (cross-compiled, no GPU needed) and travels
 to the GPU box with the repository snapshot.  Translation units are compiled in parallel:
-capi.cu (pairwise path, life cycle, probes), graph_api.cu (graph path host side) and graph_inst.cu
+capi.cu (pairwise path host side, life cycle, probes), pairwise_inst.cu once per CTA size of the pairwise kernel
+(512 / 256 / 128 threads), graph_api.cu (graph path host side) and graph_inst.cu
 once per (padded column count, padded hidden width) pair (-DCGNN_DP=8|16|20|22|24|32 -DCGNN_HP=20|32).
 """
 import os
@@ -16,12 +17,15 @@ OBJ = os.path.join(HERE, "build")
 LIB = os.path.join(HERE, "libcgnn_b200.so")
 GRAPH_DPS = (8, 16, 20, 22, 24, 32)
 GRAPH_HPS = (20, 32)
+PAIRWISE_BUILDS = ((512, 2), (256, 4), (128, 8))      # threads per CTA, CTAs per SM
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
               "-Xcompiler", "-fPIC"]
 
 
 def _units():
     u = [("capi", "capi.cu", []), ("graph_api", "graph_api.cu", [])]
+    u += [("pairwise_%d" % nt, "pairwise_inst.cu", ["-DCGNN_PW_NT=%d" % nt, "-DCGNN_PW_CTAS=%d" % ctas, "-DCGNN_PW_NS=pw%d" % nt,
+                                                     "-DCGNN_PW_TAG=%d" % nt]) for nt, ctas in PAIRWISE_BUILDS]
     u += [("graph_dp%d_hp%d" % (d, hp), "graph_inst.cu", ["-DCGNN_DP=%d" % d, "-DCGNN_HP=%d" % hp])
           for d in GRAPH_DPS for hp in GRAPH_HPS]
     return u

@@ -4,15 +4,25 @@
 #include <cmath>
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <numeric>
 #include <string>
 #include <vector>
 
 #include "ctx.h"
-#include "pairwise.cuh"
+#include "common.cuh"
+#include "pairwise_args.h"
 
 using namespace cgnn;
+
+// pairs of up to this many rows run on the 128- / 256-thread build of the pairwise kernel (measured: tools/bench_rows.py)
+#ifndef CGNN_PW_ROWS_128
+#define CGNN_PW_ROWS_128 160
+#endif
+#ifndef CGNN_PW_ROWS_256
+#define CGNN_PW_ROWS_256 640
+#endif
 
 // ---------------------------------------------------------------------------------------------
 // Pipe-peak micro-benchmarks: 8 independent dependency chains per thread, results kept live.
@@ -60,26 +70,41 @@ __global__ void __launch_bounds__(512) probe_ffma2_kernel(float* sink, int iters
     if (s == 123.456f) sink[0] = s;
 }
 
-template <int POL>
-static cudaError_t launch_pairwise(const PairwiseArgs& a, int grid, size_t smem, cudaStream_t st) {
-    cudaError_t e = cudaFuncSetAttribute(pairwise_kernel<POL>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem));
-    if (e != cudaSuccess) return e;
-    pairwise_kernel<POL><<<grid, PW_NT, smem, st>>>(a);
-    return cudaGetLastError();
-}
+// ---------------------------------------------------------------------------------------------
+// The builds of the pairwise instance kernel (pairwise_inst.cu) and the rule that picks one PER PAIR, from the pair's
+// row count alone - so a pair's score is the same whatever else shares its batch, and the same through every entry
+// point.  Short pairs get smaller CTAs and more of them per SM: a 100-row pair has 10 tile-pair units and 25 busy
+// generator threads, which 16 warps cannot share but eight 4-warp CTAs per SM can.
+#define DECL_PW(TAG)                                                                                         \
+    cudaError_t cgnn_pw_launch_##TAG(int, const PairwiseArgs&, int, size_t, cudaStream_t);                   \
+    int cgnn_pw_occupancy_##TAG(int, size_t);                                                                \
+    size_t cgnn_pw_smem_##TAG(int, int, int);
+DECL_PW(128) DECL_PW(256) DECL_PW(512)
+#undef DECL_PW
 
-static int pairwise_occupancy(int pol, size_t smem) {
-    int n = 0;
-    cudaError_t e;
-#define OCC(P_)                                                                                              \
-    case P_:                                                                                                 \
-        cudaFuncSetAttribute(pairwise_kernel<P_>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem));   \
-        e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, pairwise_kernel<P_>, PW_NT, smem);             \
-        break;
-    switch (pol) { OCC(0) OCC(1) OCC(2) OCC(3) default: e = cudaErrorInvalidValue; }
-#undef OCC
-    if (e != cudaSuccess) { cudaGetLastError(); return 0; }
-    return n;
+struct PwBuild {
+    int threads, max_rows;
+    cudaError_t (*launch)(int, const PairwiseArgs&, int, size_t, cudaStream_t);
+    int (*occupancy)(int, size_t);
+    size_t (*smem)(int, int, int);
+};
+static PwBuild g_pw_builds[3] = {
+    {128, CGNN_PW_ROWS_128, cgnn_pw_launch_128, cgnn_pw_occupancy_128, cgnn_pw_smem_128},
+    {256, CGNN_PW_ROWS_256, cgnn_pw_launch_256, cgnn_pw_occupancy_256, cgnn_pw_smem_256},
+    {512, PW_MAX_ROWS, cgnn_pw_launch_512, cgnn_pw_occupancy_512, cgnn_pw_smem_512},
+};
+static int pw_build_of(int n_rows) {
+    static bool init = false;
+    if (!init) {          // tuning hook (tools/bench_rows.py): CGNN_PW_SPLIT="a,b" moves the two thresholds
+        init = true;
+        if (const char* e = getenv("CGNN_PW_SPLIT")) {
+            int a = 0, b = 0;
+            if (sscanf(e, "%d,%d", &a, &b) == 2 && a >= 0 && b >= a) { g_pw_builds[0].max_rows = a; g_pw_builds[1].max_rows = b; }
+        }
+    }
+    for (int k = 0; k < 2; ++k)
+        if (n_rows <= g_pw_builds[k].max_rows) return k;
+    return 2;
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -182,16 +207,25 @@ static int run_pairwise_impl(cgnn_ctx* ctx, const cgnn_hparams* hp, const float*
     const int h = hp->h_layer_dim, P = 4 * h + 1;
     const int epochs = hp->train_epochs + hp->test_epochs;
 
-    // instance table, longest first (cost ~ N^2), so the tail of the persistent queue is short
+    // instance table: grouped by kernel build (a function of the pair's row count only), inside a group longest first
+    // (cost ~ N^2) so that the tail of each persistent queue is short
     std::vector<int> order(n_pairs);
     std::iota(order.begin(), order.end(), 0);
     std::stable_sort(order.begin(), order.end(), [&](int a, int b) { return nr[a] > nr[b]; });
     std::vector<int4> tab;
     tab.reserve(n_inst);
-    for (int p : order)
-        for (int r = 0; r < n_runs; ++r)
-            for (int d = 0; d < 2; ++d) tab.push_back(make_int4(p, r, d, (p * n_runs + r) * 2 + d));
-    tab.resize(n_inst);
+    int grp_first[4] = {0, 0, 0, 0}, grp_rows[3] = {0, 0, 0};
+    for (int b = 2; b >= 0; --b) {                       // 512-thread group first: the longest instances start first
+        for (int p : order) {
+            if (pw_build_of(nr[p]) != b) continue;
+            if (dbg_host && p != 0) continue;            // the parity probe runs (pair 0, run 0, direction 0) only
+            grp_rows[b] = std::max(grp_rows[b], nr[p]);
+            for (int r = 0; r < (dbg_host ? 1 : n_runs); ++r)
+                for (int d = 0; d < (dbg_host ? 1 : 2); ++d) tab.push_back(make_int4(p, r, d, (p * n_runs + r) * 2 + d));
+        }
+        grp_first[2 - b + 1] = int(tab.size());
+    }
+    // grp_first[k] .. grp_first[k+1]: instances of build 2-k
 
     PairwiseArgs a{};
     const void* dp = nullptr;
@@ -239,33 +273,40 @@ static int run_pairwise_impl(cgnn_ctx* ctx, const cgnn_hparams* hp, const float*
         if ((rc = stage_in(ctx, ctx->wz, fourier_wz, sizeof(float) * size_t(n_inst) * epochs * 3 * 7 * a.fast_k, &dp))) return rc;
         a.wz_ext = static_cast<const float*>(dp);
     }
-    a.n_inst = n_inst; a.ld_rows = ld_rows; a.np_max = 32 * ((max_n + 31) / 32);
+    a.ld_rows = ld_rows;
     a.h = h; a.train_epochs = hp->train_epochs; a.test_epochs = hp->test_epochs; a.trace_every = hp->trace_every;
     a.lr = hp->learning_rate; a.init_std = hp->init_std;
     a.key = make_uint2((unsigned int)(hp->seed & 0xffffffffu), (unsigned int)(hp->seed >> 32));
     a.uid_base = uid_base;
-
-    const size_t smem = pw_smem_bytes(a.np_max, h, a.fast_k);
-    if (smem > size_t(ctx->prop.sharedMemPerBlockOptin))
-        return fail(ctx, CGNN_ERR_LIMIT, "instance needs %zu B of shared memory, device allows %zu", smem,
-                    size_t(ctx->prop.sharedMemPerBlockOptin));
     const int pol = hp->exp_policy < 0 ? CGNN_EXP_POLICY_PAIRWISE : hp->exp_policy;
-    int per_sm = pairwise_occupancy(pol, smem);
-    if (per_sm < 1) return fail(ctx, CGNN_ERR_CUDA, "pairwise kernel cannot be resident (smem %zu B)", smem);
-    ctx->pw_ctas_per_sm = per_sm;
-    const int grid = std::min(n_inst, per_sm * ctx->prop.multiProcessorCount);
+
+    // one launch per kernel build that has instances, back to back on the stream
+    struct Launch { int build, first, count, grid; size_t smem; int np_max; };
+    std::vector<Launch> launches;
+    for (int k = 0; k < 3; ++k) {
+        const int b = 2 - k, first = grp_first[k], count = grp_first[k + 1] - grp_first[k];
+        if (count == 0) continue;
+        const int np_max = 32 * ((grp_rows[b] + 31) / 32);
+        const size_t smem = g_pw_builds[b].smem(np_max, h, a.fast_k);
+        if (smem > size_t(ctx->prop.sharedMemPerBlockOptin))
+            return fail(ctx, CGNN_ERR_LIMIT, "instance needs %zu B of shared memory, device allows %zu", smem,
+                        size_t(ctx->prop.sharedMemPerBlockOptin));
+        const int per_sm = g_pw_builds[b].occupancy(pol, smem);
+        if (per_sm < 1) return fail(ctx, CGNN_ERR_CUDA, "pairwise kernel cannot be resident (smem %zu B)", smem);
+        if (b == 2 || launches.empty()) ctx->pw_ctas_per_sm = per_sm;
+        launches.push_back(Launch{b, first, count, std::min(count, per_sm * ctx->prop.multiProcessorCount), smem, np_max});
+    }
 
     CU(cudaEventRecord(ctx->ev0, ctx->stream));
-    cudaError_t le = cudaErrorInvalidValue;
-    switch (pol) {
-        case 0: le = launch_pairwise<0>(a, grid, smem, ctx->stream); break;
-        case 1: le = launch_pairwise<1>(a, grid, smem, ctx->stream); break;
-        case 2: le = launch_pairwise<2>(a, grid, smem, ctx->stream); break;
-        case 3: le = launch_pairwise<3>(a, grid, smem, ctx->stream); break;
+    for (size_t k = 0; k < launches.size(); ++k) {
+        const Launch& L = launches[k];
+        PairwiseArgs ak = a;
+        ak.inst = a.inst + L.first; ak.n_inst = L.count; ak.np_max = L.np_max; ak.counter = a.counter + 16 * int(k);
+        const cudaError_t le = g_pw_builds[L.build].launch(pol, ak, L.grid, L.smem, ctx->stream);
+        if (le != cudaSuccess) return fail(ctx, CGNN_ERR_CUDA, "pairwise kernel launch: %s", cudaGetErrorString(le));
     }
-    if (le != cudaSuccess) return fail(ctx, CGNN_ERR_CUDA, "pairwise kernel launch: %s", cudaGetErrorString(le));
     CU(cudaEventRecord(ctx->ev1, ctx->stream));
-    ctx->last_launches = 1;
+    ctx->last_launches = int(launches.size());
 
     if ((rc = copy_back(ctx, scores, a.scores, sizeof(float) * n_inst))) return rc;
     if ((rc = copy_back(ctx, loss_trace, a.trace, sizeof(float) * size_t(n_inst) * epochs))) return rc;
@@ -447,19 +488,14 @@ static int noalloc_impl(int device, void* stream, const cgnn_hparams* hp, const 
     a.scores = d_scores;
     a.fast_k = hp->fast_mmd_vectors;
 
-    const size_t smem = pw_smem_bytes(a.np_max, a.h, a.fast_k);
+    const PwBuild& B = g_pw_builds[pw_build_of(n_rows)];     // the same per-pair rule as cgnn_b200_run_pairwise: identical scores
+    const size_t smem = B.smem(a.np_max, a.h, a.fast_k);
     if (smem > size_t(smem_optin)) return na_fail(errbuf, errbuf_len, CGNN_ERR_LIMIT, "instance needs %zu B of shared memory", smem);
     const int pol = hp->exp_policy < 0 ? CGNN_EXP_POLICY_PAIRWISE : hp->exp_policy;
-    const int per_sm = pairwise_occupancy(pol, smem);
+    const int per_sm = B.occupancy(pol, smem);
     if (per_sm < 1) return na_fail(errbuf, errbuf_len, CGNN_ERR_CUDA, "pairwise kernel cannot be resident");
     const int grid = std::min(n_inst, per_sm * n_sm);
-    cudaError_t le = cudaErrorInvalidValue;
-    switch (pol) {
-        case 0: le = launch_pairwise<0>(a, grid, smem, st); break;
-        case 1: le = launch_pairwise<1>(a, grid, smem, st); break;
-        case 2: le = launch_pairwise<2>(a, grid, smem, st); break;
-        case 3: le = launch_pairwise<3>(a, grid, smem, st); break;
-    }
+    const cudaError_t le = B.launch(pol, a, grid, smem, st);
     if (le != cudaSuccess) return na_fail(errbuf, errbuf_len, CGNN_ERR_CUDA, "pairwise kernel launch: %s", cudaGetErrorString(le));
     NA_CU(cudaStreamSynchronize(st));
     return CGNN_OK;

@@ -33,10 +33,21 @@
 // that is rotated with one shuffle per step, so after 32 steps lane l owns column l's total, flushed
 // with one fixed-point shared atomic.  Diagonal tiles use a "duo" walk (PP(i,j), PT(i,j)) over all
 // ordered pairs.  Per evaluation: ~25 issue slots of which 3-7 MUFU (policy dependent).
+//
+// The same source is compiled three times (pairwise_inst.cu: -DCGNN_PW_NT=512|256|128 threads per CTA with 2|4|8 CTAs per
+// SM, each in its own namespace): a 100-row pair has 10 tile-pair units and 25 busy generator threads - 16 warps
+// cannot share that, four CTAs of 8 warps (or eight of 4) per SM can.  The host picks the build per PAIR from its row
+// count alone, so a pair's score never depends on what else is in the batch.
 #pragma once
 #include "common.cuh"
+#include "pairwise_args.h"
+
+#ifndef CGNN_PW_NS
+#define CGNN_PW_NS pw512
+#endif
 
 namespace cgnn {
+namespace CGNN_PW_NS {
 
 #ifndef CGNN_PW_NT
 #define CGNN_PW_NT 512
@@ -52,30 +63,8 @@ namespace cgnn {
 constexpr int PW_NT = CGNN_PW_NT;       // threads per CTA
 constexpr int PW_NW = PW_NT / 32;       // warps per CTA
 constexpr int PW_MIN_CTAS = CGNN_PW_CTAS;
-constexpr int PW_MAX_ROWS = 2048;
 constexpr float PW_PAD = 1.0e15f;
 
-struct PairwiseArgs {
-    const float* xy;          // [n_pairs][ld_rows][2]
-    const int*   n_rows;      // [n_pairs]
-    const int4*  inst;        // [n_inst] (pair, run, dir, out_index), sorted by decreasing cost
-    int n_inst, ld_rows, np_max;
-    int h, train_epochs, test_epochs, trace_every;
-    float lr, init_std;
-    uint2 key;                  // Philox key = seed; the high half of the 64-bit instance uid is xor-ed into key.y
-    unsigned long long uid_base;
-    const float* noise;       // NULL or [n_inst][epochs][ld_rows]   (indexed by out_index)
-    const float* init_params; // NULL or [n_inst][4h+1]
-    float* scores;            // [n_inst] by out_index
-    float* trace;             // NULL or [n_inst][train+test]
-    float* params_out;        // NULL or [n_inst][4h+1]
-    int*   counter;           // work queue head (scratch)
-    // parity probe (single instance): any may be NULL
-    float *dbg_loss, *dbg_yhat, *dbg_dldy, *dbg_grad, *dbg_params;
-    // random-feature ("Fourier") MMD, Loss.py:35-56 (SETTINGS.use_Fast_MMD): fast_k = nb_vectors_approx_MMD, 0 = off
-    int fast_k;
-    const float* wz_ext;      // NULL (in-kernel Philox) or [n_inst][epochs][3][7*fast_k]: the matrix of Loss.py:35-37
-};
 
 struct PwSmem {
     float4* Qd; float* xs; float* es; float* yh; long long* g64; unsigned short* rank;
@@ -661,4 +650,5 @@ __global__ void __launch_bounds__(PW_NT, PW_MIN_CTAS) pairwise_kernel(const Pair
     }
 }
 
+}  // namespace CGNN_PW_NS
 }  // namespace cgnn

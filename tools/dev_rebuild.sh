@@ -10,6 +10,7 @@ for v in "$@"; do
   nvcc $FLAGS -DCGNN_DP=$dp -DCGNN_HP=$hp $EXTRA -c csrc/graph_inst.cu -o build/graph_dp${dp}_hp${hp}.o & pids+=($!)
 done
 nvcc $FLAGS -c csrc/capi.cu -o build/capi.o & pids+=($!)
+if [ -n "$PW" ]; then for v in "512 2" "256 4" "128 8"; do set -- $v; nvcc $FLAGS -DCGNN_PW_NT=$1 -DCGNN_PW_CTAS=$2 -DCGNN_PW_NS=pw$1 -DCGNN_PW_TAG=$1 -c csrc/pairwise_inst.cu -o build/pairwise_$1.o & pids+=($!); done; fi
 nvcc $FLAGS -c csrc/graph_api.cu -o build/graph_api.o & pids+=($!)
 for p in "${pids[@]}"; do wait $p; done
 nvcc -shared -o libcgnn_b200.so build/*.o
