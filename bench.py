@@ -269,6 +269,7 @@ def hill_climbing_leg(world, barrier, max_over_ranks):
     return {"config": "BASELINE configs[4]: synthetic 20-variable DAG, n=2000 -> 1500 rows per run, nb_runs=16, h=20, 1000+500 epochs",
             "api": "cgnn_b200.GNN.orient_graph + cgnn_b200.CGNN.orient_directed_graph (host DataFrame in, graph out)",
             "scaling": "strong", "n_gpus": world, "seconds_pairwise_orientation": s_pw, "seconds_hill_climbing": s_hc,
+            "seconds_in_kernels_rank0": float(getattr(hill_climbing, "last_kernel_seconds", 0.0)),
             "candidate_graphs_scored": n_graphs, "candidate_graphs_per_s": n_graphs / s_hc,
             "graph_train_steps_per_s": n_graphs * 16 * 1000 / s_hc, "batches": batches,
             "instances_per_launch_per_rank": [int(-(-b // world) * 16) for b in batches],

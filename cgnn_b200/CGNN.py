@@ -104,6 +104,7 @@ def hill_climbing(graph, data, run_cgnn_function=run_CGNN_b200, **kwargs):
         final = run_search(_climb, graph, scorer)
         graph._graph = final._graph                              # same object mutated, like the reference
         hill_climbing.last_batches = list(scorer.batches)
+        hill_climbing.last_kernel_seconds = scorer.kernel_ms * 1e-3
         return graph
     return _climb(graph, _FunctionScorer(data, run_cgnn_function, **kwargs))
 

@@ -126,6 +126,7 @@ def hill_climbing_confounders(graph, data, run_cgnn_function=run_CGNN_confounder
         final = run_search(_climb_confounders, graph, scorer)
         graph._graph = final._graph
         hill_climbing_confounders.last_batches = list(scorer.batches)
+        hill_climbing_confounders.last_kernel_seconds = scorer.kernel_ms * 1e-3
         return graph
     return _climb_confounders(graph, _FunctionScorer(data, run_cgnn_function, penalty=True, **kwargs))
 

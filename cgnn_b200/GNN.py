@@ -43,6 +43,16 @@ def _staging(shape):
     return np.zeros(shape, np.float32)
 
 
+def print_progress(trace, train_epochs, every, ident):
+    """The reference's progress lines (GNN.py:98-102,119-121; CGNN.py:123-127): one per instance and `every`-th
+    iteration of training (the pre-update loss) and of evaluation.  trace: [n_inst, train+test]; ident(k) -> (idx, run)."""
+    for k in range(trace.shape[0]):
+        idx, run = ident(k)
+        for part, lo, hi in (("train", 0, train_epochs), ("test", train_epochs, trace.shape[1])):
+            for it in range(0, hi - lo, every):
+                print("Pair:{}, Run:{}, Iter:{}, score:{}".format(idx, run, it, trace[k, lo + it]))
+
+
 def score_pairs(pairs, idx0=0, **kwargs):
     """Per-run direction scores of a list of [N,2] float32 matrices: array [n_pairs, nb_runs, 2]
     (A->B, B->A).  The batched replacement of `[tf_run_instance(m, idx, run) for run in range(nb_runs)]`
@@ -65,10 +75,23 @@ def score_pairs(pairs, idx0=0, **kwargs):
     for k, m in enumerate(slots):
         xy[k, :m.shape[0]] = m
         n_rows[k] = m.shape[0]
-    kw = {k: v for k, v in kwargs.items() if k not in ("nb_runs", "nb_jobs", "n_runs")}
+    kw = {k: v for k, v in kwargs.items() if k not in ("nb_runs", "nb_jobs", "n_runs", "verbose")}
+    progress = bool(kwargs.get("verbose", SETTINGS.verbose))      # GNN.py:98-102,119-121: a line every 100 iterations
+    if progress:
+        kw.setdefault("trace_every", 100)
 
     def call(engine, lo, hi, uid):
-        return engine.run_pairwise(xy[lo:hi], n_rows=n_rows[lo:hi], n_runs=runs_per_slot, uid_base=uid, **kw)["scores"]
+        r = engine.run_pairwise(xy[lo:hi], n_rows=n_rows[lo:hi], n_runs=runs_per_slot, uid_base=uid, want_trace=progress, **kw)
+        if progress and r.get("trace") is not None:
+
+            def ident(k):                       # trace row k of this call -> (pair index, run) as the reference numbers them
+                slot = lo + k // (2 * runs_per_slot)
+                if runs_per_slot > 1:
+                    return idx0 + slot, (k // 2) % runs_per_slot
+                return idx0 + slot // nb_runs, slot % nb_runs
+
+            print_progress(r["trace"], int(kw.get("train_epochs", SETTINGS.train_epochs)), 100, ident)
+        return r["scores"]
 
     uid0 = int(kwargs.get("uid_base", 0)) + idx0 * nb_runs * 2
     kw.pop("uid_base", None)

@@ -18,10 +18,10 @@ using namespace cgnn;
 
 // pairs of up to this many rows run on the 128- / 256-thread build of the pairwise kernel (measured: tools/bench_rows.py)
 #ifndef CGNN_PW_ROWS_128
-#define CGNN_PW_ROWS_128 160
+#define CGNN_PW_ROWS_128 256
 #endif
 #ifndef CGNN_PW_ROWS_256
-#define CGNN_PW_ROWS_256 640
+#define CGNN_PW_ROWS_256 704
 #endif
 
 // ---------------------------------------------------------------------------------------------

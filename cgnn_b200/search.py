@@ -61,6 +61,8 @@ class GraphScorer(object):
         self.cache = {}
         self.pending = None          # list of graphs while speculating
         self.batches = []            # sizes of the engine batches (diagnostics)
+        self.kernel_ms = 0.0         # device time of this process's share of the batches
+        self.n_scored = 0            # candidates scored so far: the `idx` of the reference's progress lines
         self.horizon = int(kwargs.get("speculation_horizon", 0)) or None
 
     def _bind(self, graph):
@@ -140,11 +142,23 @@ class GraphScorer(object):
                 subsets = np.stack([
                     np.random.default_rng([int(SETTINGS.seed), uids[g] >> 8, r, 0xC6]).permutation(n_total)[:cap]
                     for g in range(lo, hi) for r in range(nb_runs)]).astype(np.int32)
+            kw = dict(self.kwargs)
+            progress = bool(kw.pop("verbose", SETTINGS.verbose))
+            every = 500 if self.confounders else 100            # CGNN.py:123-127, CGNN_confounders.py:142-146
+            if progress:
+                kw.setdefault("trace_every", every)
             r = engine.run_graph(self.data, plans[lo:hi], n_runs=nb_runs, row_subsets=subsets,
-                                 graph_uids=uids[lo:hi], **self.kwargs)
+                                 graph_uids=uids[lo:hi], want_trace=progress, **kw)
+            self.kernel_ms += float(getattr(engine, "last_kernel_ms", 0.0))
+            if progress and r.get("trace") is not None:
+                from .GNN import print_progress
+                print_progress(r["trace"], int(kw.get("train_epochs", SETTINGS.train_epochs)), every,
+                               lambda k: (self.n_scored + lo + k // nb_runs, k % nb_runs))
             return r["scores"]
 
-        return runtime.run_sharded(len(plans), 0, 0, call, tail_shape=(nb_runs,))
+        out = runtime.run_sharded(len(plans), 0, 0, call, tail_shape=(nb_runs,))
+        self.n_scored += len(plans)
+        return out
 
 
 def _run_scores_single(self, plan, uid):
