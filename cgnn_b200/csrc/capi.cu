@@ -70,6 +70,44 @@ __global__ void __launch_bounds__(512) probe_ffma2_kernel(float* sink, int iters
     if (s == 123.456f) sink[0] = s;
 }
 
+// FADD2 alone, and the FMA-pipe instruction mix of the graph kernel's gradient loop (per coordinate pair: one FADD2
+// difference, one FFMA2 square-accumulate, one FFMA2 with a scalar weight broadcast over the pair), all operands in
+// registers: what the FMA pipe sustains on exactly these instruction forms.
+__global__ void __launch_bounds__(512) probe_fadd2_kernel(float* sink, int iters) {
+    float2 x[8];
+    const float2 b = splat2(1e-3f + 1e-6f * float(threadIdx.x & 31));
+#pragma unroll
+    for (int k = 0; k < 8; ++k) x[k] = make_float2(0.1f * float(k + 1), 0.05f * float(k + 1));
+    for (int it = 0; it < iters; ++it) {
+#pragma unroll
+        for (int k = 0; k < 8; ++k) x[k] = fadd2(x[k], b);
+    }
+    float s = 0.f;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) s += x[k].x + x[k].y;
+    if (s == 123.456f) sink[0] = s;
+}
+__global__ void __launch_bounds__(512) probe_mix_kernel(float* sink, int iters) {
+    float2 p[4], acc[4], e[4];
+    float w = 0.5f + 1e-3f * float(threadIdx.x & 31);
+#pragma unroll
+    for (int k = 0; k < 4; ++k) { p[k] = make_float2(0.1f * float(k + 1), 0.07f * float(k + 1)); acc[k] = e[k] = make_float2(0.f, 0.f); }
+    float2 t = make_float2(0.3f, 0.2f);
+    for (int it = 0; it < iters; ++it) {
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            const float2 d = fadd2(t, p[k]);                 // difference
+            e[k] = ffma2(d, d, e[k]);                        // squared distance
+            acc[k] = ffma2(splat2(w), d, acc[k]);            // weighted accumulation
+        }
+        t.x = t.x * 0.999f; w = w * 0.9999f;                 // keeps the loop from being hoisted (2 scalar ops per 12 packed)
+    }
+    float s = 0.f;
+#pragma unroll
+    for (int k = 0; k < 4; ++k) s += acc[k].x + acc[k].y + e[k].x + e[k].y;
+    if (s == 123.456f) sink[0] = s;
+}
+
 // ---------------------------------------------------------------------------------------------
 // The builds of the pairwise instance kernel (pairwise_inst.cu) and the rule that picks one PER PAIR, from the pair's
 // row count alone - so a pair's score is the same whatever else shares its batch, and the same through every entry
@@ -344,7 +382,7 @@ int cgnn_b200_pairwise_step_debug(cgnn_ctx* ctx, const cgnn_hparams* hp, const f
 
 int cgnn_b200_probe_peak(cgnn_ctx* ctx, int kind, int reps, double* out_per_second) {
     if (!ctx || !out_per_second) return CGNN_ERR_ARG;
-    if (kind < 0 || kind > 2) return fail(ctx, CGNN_ERR_ARG, "probe kind %d unknown", kind);
+    if (kind < 0 || kind > 4) return fail(ctx, CGNN_ERR_ARG, "probe kind %d unknown", kind);
     CU(cudaSetDevice(ctx->device));
     int rc = ensure(ctx, ctx->counter, 256);
     if (rc) return rc;
@@ -354,13 +392,16 @@ int cgnn_b200_probe_peak(cgnn_ctx* ctx, int kind, int reps, double* out_per_seco
         CU(cudaEventRecord(ctx->ev0, ctx->stream));
         if (kind == 0)      probe_mufu_kernel<<<grid, nt, 0, ctx->stream>>>(static_cast<float*>(ctx->counter.p), iters);
         else if (kind == 1) probe_ffma_kernel<<<grid, nt, 0, ctx->stream>>>(static_cast<float*>(ctx->counter.p), iters);
-        else                probe_ffma2_kernel<<<grid, nt, 0, ctx->stream>>>(static_cast<float*>(ctx->counter.p), iters);
+        else if (kind == 2) probe_ffma2_kernel<<<grid, nt, 0, ctx->stream>>>(static_cast<float*>(ctx->counter.p), iters);
+        else if (kind == 3) probe_fadd2_kernel<<<grid, nt, 0, ctx->stream>>>(static_cast<float*>(ctx->counter.p), iters);
+        else                probe_mix_kernel<<<grid, nt, 0, ctx->stream>>>(static_cast<float*>(ctx->counter.p), iters);
         CU(cudaGetLastError());
         CU(cudaEventRecord(ctx->ev1, ctx->stream));
         CU(cudaStreamSynchronize(ctx->stream));
         float ms = 0.f;
         CU(cudaEventElapsedTime(&ms, ctx->ev0, ctx->ev1));
-        const double ops = double(grid) * nt * double(iters) * 8.0 * (kind == 0 ? 1.0 : kind == 1 ? 2.0 : 4.0);
+        // kinds 3 and 4 report packed INSTRUCTIONS x 2 lanes per second ("lane-slots": an FFMA2 = 2), i.e. half the flop/s of kind 2
+        const double ops = double(grid) * nt * double(iters) * (kind == 0 ? 8.0 : kind == 1 ? 16.0 : kind == 2 ? 32.0 : kind == 3 ? 16.0 : 24.0);
         if (r > 0) best = std::max(best, ops / (double(ms) * 1e-3));
     }
     *out_per_second = best;

@@ -44,7 +44,10 @@ namespace cg = cooperative_groups;
 #define GR_GRAD_UNROLL
 #endif
 
-constexpr int GR_NT = 512;
+#ifndef CGNN_GR_NT
+#define CGNN_GR_NT 512
+#endif
+constexpr int GR_NT = CGNN_GR_NT;
 constexpr int GR_MAX_CLUSTER = 8;
 constexpr int GR_NW = GR_NT / 32;
 constexpr int GR_MAX_VAR = 32;

@@ -104,7 +104,7 @@ class Engine:
     def probe_peak(self, kind, reps=5):
         """kind 'mufu' -> exp/s, 'ffma' / 'ffma2' -> flop/s of scalar / packed (FP32x2) FMA chains (micro-benchmarks)."""
         out = C.c_double()
-        k = {"mufu": 0, "ffma": 1, "ffma2": 2}[kind]
+        k = {"mufu": 0, "ffma": 1, "ffma2": 2, "fadd2_slots": 3, "graph_mix_slots": 4}[kind]
         self._check(self._lib.cgnn_b200_probe_peak(self._h, k, reps, C.byref(out)), "probe_peak")
         return out.value
 

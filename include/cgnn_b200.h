@@ -253,7 +253,9 @@ int  cgnn_b200_run_pairwise_noalloc(int device, void* stream, const cgnn_hparams
 
 /* Micro-benchmarks that measure this chip's own pipe peaks (MEASURED_PEAKS.json holds only HBM
  * and bf16 tensor numbers): kind 0 = MUFU ex2.approx.ftz.f32 (result in exp/s),
- * kind 1 = FP32 FFMA (result in flop/s, 2 per FFMA).  Best of `reps` launches. */
+ * kind 1 = FP32 FFMA (result in flop/s, 2 per FFMA), kind 2 = packed FFMA2 / fma.rn.f32x2 (flop/s, 4 per instruction),
+ * kind 3 = packed FADD2 and kind 4 = the FMA-pipe instruction mix of the graph kernel's gradient loop (both in
+ * FMA-pipe lane-slots per second: 2 per packed instruction and lane).  Best of `reps` launches. */
 int  cgnn_b200_probe_peak(cgnn_ctx* ctx, int kind, int reps, double* out_per_second);
 
 /* Number of SMs of the context's device and persistent CTAs per SM the engine launches. */
