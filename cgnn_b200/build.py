@@ -4,7 +4,8 @@ The shared library is the product; it is built here (cross-compiled, no GPU need
 to the GPU box with the repository snapshot.  Translation units are compiled in parallel:
 capi.cu (pairwise path host side, life cycle, probes), pairwise_inst.cu once per CTA size of the pairwise kernel
 (512 / 256 / 128 threads), graph_api.cu (graph path host side) and graph_inst.cu
-once per (padded column count, padded hidden width) pair (-DCGNN_DP=8|16|20|22|24|32 -DCGNN_HP=20|32).
+once per (padded column count, padded hidden width, noise mode) (-DCGNN_DP=8|16|20|22|24|32 -DCGNN_HP=20|32
+-DCGNN_REGEN=0|1).
 """
 import os
 import shutil
@@ -26,8 +27,9 @@ def _units():
     u = [("capi", "capi.cu", []), ("graph_api", "graph_api.cu", [])]
     u += [("pairwise_%d" % nt, "pairwise_inst.cu", ["-DCGNN_PW_NT=%d" % nt, "-DCGNN_PW_CTAS=%d" % ctas, "-DCGNN_PW_NS=pw%d" % nt,
                                                      "-DCGNN_PW_TAG=%d" % nt]) for nt, ctas in PAIRWISE_BUILDS]
-    u += [("graph_dp%d_hp%d" % (d, hp), "graph_inst.cu", ["-DCGNN_DP=%d" % d, "-DCGNN_HP=%d" % hp])
-          for d in GRAPH_DPS for hp in GRAPH_HPS]
+    u += [("graph_dp%d_hp%d%s" % (d, hp, "_regen" if rg else ""), "graph_inst.cu",
+           ["-DCGNN_DP=%d" % d, "-DCGNN_HP=%d" % hp, "-DCGNN_REGEN=%d" % rg])
+          for rg in (0, 1) for d in GRAPH_DPS for hp in GRAPH_HPS]
     return u
 
 

@@ -267,35 +267,25 @@ __device__ __forceinline__ float2 ksum_p2(float2 Dp) {
 // ---------------------------------------------------------------------------------------------
 template <int POL>
 __device__ __forceinline__ float2 wsum_r2(float2 D) {
-    // all ex2 arguments first, then the (independent) MUFU ops back to back, then two short chains that meet at the
-    // end: the dependent path is one FMUL2, one ex2 and four FP32x2 operations
-    const float2 a0 = fmul2(D, splat2(C0)), a2 = fmul2(D, splat2(C2));
-    const float2 a6 = ffma2(D, splat2(C6), splat2(CGNN_LOG2_50));
-    float2 a1, a3, a4, a5;
-    if (POL < 2) a1 = fmul2(D, splat2(C1));
-    if (POL < 3) a5 = fmul2(D, splat2(C5));
-    if (POL == 0) { a3 = fmul2(D, splat2(C3)); a4 = fmul2(D, splat2(C4)); }
-    const float2 p = ex2f2(a2), q = ex2f2(a0), k6w = ex2f2(a6);                  // k6w = 50 * k(50)
-    float2 k1, k5, k3, k4;
-    if (POL < 2) k1 = ex2f2(a1);
-    if (POL < 3) k5 = ex2f2(a5);
-    if (POL == 0) { k3 = ex2f2(a3); k4 = ex2f2(a4); }
-    float2 u;                                                                   // 50 k6 + G0 q + G1 k1 (+ G5 k5)
+    const float2 q = ex2f2(fmul2(D, splat2(C0)));
+    const float2 p = ex2f2(fmul2(D, splat2(C2)));
+    float2 w = ex2f2(ffma2(D, splat2(C6), splat2(CGNN_LOG2_50)));               // 50 * k(50)
     if (POL >= 2) {
         const float2 q2 = fmul2(q, q), q4 = fmul2(q2, q2), q8 = fmul2(q4, q4);
-        u = ffma2(ffma2(splat2(G1), fmul2(q8, q), splat2(G0)), q, k6w);
+        w = ffma2(ffma2(splat2(G1), fmul2(q8, q), splat2(G0)), q, w);
     } else {
-        u = ffma2(splat2(G1), k1, ffma2(splat2(G0), q, k6w));
+        w = ffma2(splat2(G1), ex2f2(fmul2(D, splat2(C1))), ffma2(splat2(G0), q, w));
     }
-    float2 w;
     if (POL >= 1) {
         const float2 p2 = fmul2(p, p);
-        if (POL >= 3) { const float2 p4 = fmul2(p2, p2), p8 = fmul2(p4, p4); u = ffma2(splat2(G5), fmul2(fmul2(p8, p8), p4), u); }
-        else u = ffma2(splat2(G5), k5, u);
-        w = ffma2(ffma2(fadd2(p2, splat2(G3)), p, splat2(G2)), p, u);            // G2 p + G3 p^2 + p^4   (G4 == 1)
+        w = ffma2(ffma2(fadd2(p2, splat2(G3)), p, splat2(G2)), p, w);
+        if (POL >= 3) { const float2 p4 = fmul2(p2, p2), p8 = fmul2(p4, p4); w = ffma2(splat2(G5), fmul2(fmul2(p8, p8), p4), w); }
+        else w = ffma2(splat2(G5), ex2f2(fmul2(D, splat2(C5))), w);
     } else {
-        u = ffma2(splat2(G5), k5, u);
-        w = fadd2(ffma2(splat2(G3), k3, ffma2(splat2(G2), p, u)), k4);
+        w = ffma2(splat2(G2), p, w);
+        w = ffma2(splat2(G3), ex2f2(fmul2(D, splat2(C3))), w);
+        w = fadd2(w, ex2f2(fmul2(D, splat2(C4))));
+        w = ffma2(splat2(G5), ex2f2(fmul2(D, splat2(C5))), w);
     }
     return w;
 }

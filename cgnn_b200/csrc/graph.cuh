@@ -136,21 +136,25 @@ __host__ __device__ inline size_t gr_smem_bytes(int NP, int DP, int nbuf_cols, i
 struct GrNoise {
     const float* nb;           // the warp's buffer [column][32 lanes] (buffered mode)
     const float* ext;          // caller-supplied noise of the step [column][N], or NULL
-    int regen, i, N, lane;
+    int i, N, lane;
     unsigned int step, uid;
     uint2 key;
 };
-__device__ __forceinline__ float gr_noise_get(const GrNoise& z, int c) {
-    if (!z.regen) return z.nb[c * 32 + z.lane];
-    if (z.ext) return (z.i < z.N) ? z.ext[size_t(c) * z.N + z.i] : 0.f;
-    const float4 n = normal4(philox4x32_10(make_uint4(z.i, z.step, GR_STREAM_NOISE0 + (c >> 2), z.uid), z.key));
+static __device__ __noinline__ float gr_noise_regen(const float* ext, int i, int N, unsigned int step, unsigned int uid, unsigned int kx,
+                                             unsigned int ky, int c) {
+    if (ext) return (i < N) ? ext[size_t(c) * N + i] : 0.f;
+    const float4 n = normal4(philox4x32_10(make_uint4(i, step, GR_STREAM_NOISE0 + (c >> 2), uid), make_uint2(kx, ky)));
     const int e = c & 3;
     return e == 0 ? n.x : e == 1 ? n.y : e == 2 ? n.z : n.w;
+}
+template <bool REGEN>
+__device__ __forceinline__ float gr_noise_get(const GrNoise& z, int c) {
+    if (!REGEN) return z.nb[c * 32 + z.lane];
+    return gr_noise_regen(z.ext, z.i, z.N, z.step, z.uid, z.key.x, z.key.y, c);
 }
 
 __device__ __forceinline__ void gr_fill_noise(const GrSmem& s, const GraphArgs& a, float* nb, int i, int lane, int step,
                                               unsigned int uid, uint2 key, const float* noise_step) {
-    if (a.noise_regen) return;
     const int nn = s.desc->n_noise;
     if (noise_step) {
         for (int c = 0; c < nn; ++c) nb[c * 32 + lane] = (i < a.N) ? noise_step[size_t(c) * a.N + i] : 0.f;
@@ -165,7 +169,7 @@ __device__ __forceinline__ void gr_fill_noise(const GrSmem& s, const GraphArgs& 
 }
 
 // hidden pre-activations of node k for this lane's row: z[kk] = b_in[kk] + sum_p u_p W_in[p][kk], as HP/2 pairs
-template <int DP, int HP>
+template <int DP, int HP, bool REGEN>
 __device__ __forceinline__ void gr_node_z(const GrSmem& s, const GrNoise& nz, int k, int i, float2 (&z)[HP / 2]) {
     const GraphDesc& g = *s.desc;
     const float* th = s.theta + g.pad_off[k];
@@ -175,7 +179,7 @@ __device__ __forceinline__ void gr_node_z(const GrSmem& s, const GrNoise& nz, in
 #pragma unroll
     for (int q = 0; q < HP / 4; ++q) { const float4 b = b4[q]; z[2 * q] = make_float2(b.x, b.y); z[2 * q + 1] = make_float2(b.z, b.w); }
     for (int p = 0; p < n_in; ++p) {
-        const float2 u = splat2((p < n_par) ? s.Pm[i * DP + idx[p]] : gr_noise_get(nz, idx[p]));
+        const float2 u = splat2((p < n_par) ? s.Pm[i * DP + idx[p]] : gr_noise_get<REGEN>(nz, idx[p]));
         const float4* w4 = reinterpret_cast<const float4*>(th + p * HP);
 #pragma unroll
         for (int q = 0; q < HP / 4; ++q) {
@@ -187,12 +191,12 @@ __device__ __forceinline__ void gr_node_z(const GrSmem& s, const GrNoise& nz, in
 }
 
 // Generator forward of one row block (CGNN.py:63-84), nodes in build order.
-template <int DP, int HP>
+template <int DP, int HP, bool REGEN>
 __device__ __forceinline__ void gr_forward_block(const GrSmem& s, const GrNoise& nz, int i) {
     const GraphDesc& g = *s.desc;
     for (int k = 0; k < g.n_var; ++k) {
         float2 z[HP / 2];
-        gr_node_z<DP, HP>(s, nz, k, i, z);
+        gr_node_z<DP, HP, REGEN>(s, nz, k, i, z);
         const float* w_out = s.theta + g.pad_off[k] + (g.n_in[k] + 1) * HP;
         const float4* w4 = reinterpret_cast<const float4*>(w_out);
         float2 acc = make_float2(w_out[HP], 0.f);                       // b_out
@@ -423,12 +427,12 @@ __device__ __forceinline__ float gr_zget(const float2 (&z)[HP / 2], int kk) {
 
 // Thread-local backward of one row through all nodes in reverse build order; parameter gradients are
 // reduced over the 32 rows of the block (warp_reduce32) and added to the shared fixed-point accumulators.
-template <int DP, int HP>
+template <int DP, int HP, bool REGEN>
 __device__ __forceinline__ void gr_backward_block(const GrSmem& s, const GrNoise& nz, int i, int lane, float* gl) {
     const GraphDesc& g = *s.desc;
     for (int k = g.n_var - 1; k >= 0; --k) {
         float2 z[HP / 2];
-        gr_node_z<DP, HP>(s, nz, k, i, z);
+        gr_node_z<DP, HP, REGEN>(s, nz, k, i, z);
         const int n_in = g.n_in[k], n_par = g.n_par[k];
         const int off = g.pad_off[k];
         const short* idx = g.in_idx + g.in_off[k];
@@ -458,7 +462,7 @@ __device__ __forceinline__ void gr_backward_block(const GrSmem& s, const GrNoise
         if (has_slot) fx_add(&s.g64[off + n_in * HP + slot], double(r));
         // W_in rows and input gradients
         for (int p = 0; p < n_in; ++p) {
-            const float u = (p < n_par) ? s.Pm[i * DP + idx[p]] : gr_noise_get(nz, idx[p]);
+            const float u = (p < n_par) ? s.Pm[i * DP + idx[p]] : gr_noise_get<REGEN>(nz, idx[p]);
 #pragma unroll
             for (int kk = 0; kk < HP; ++kk) v[kk] = u * gr_zget<HP>(z, kk);
             r = warp_reduce_n<HP>(v, lane, slot, has_slot);
@@ -610,7 +614,9 @@ __device__ __forceinline__ double gr_cluster_sum(double v, double* red, int warp
     return tot;
 }
 
-template <int DP, int HP, int POL>
+// REGEN (noise re-derived at every use, GraphArgs::noise_regen) is a separate instantiation of the whole kernel: the
+// common buffered-noise kernel then carries no trace of it (a runtime switch cost it 2-5 % through register allocation).
+template <int DP, int HP, int POL, bool REGEN>
 __global__ void __launch_bounds__(GR_NT, 1) graph_kernel(const GraphArgs a) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     __shared__ int s_inst;
@@ -729,8 +735,8 @@ __global__ void __launch_bounds__(GR_NT, 1) graph_kernel(const GraphArgs a) {
             // ---- generator forward, all rows ------------------------------------------------
             for (int rb = warp; rb < NB; rb += GR_NW) {
                 const int i = 32 * rb + lane;
-                gr_fill_noise(s, a, nb, i, lane, it, uid, key, noise_step);
-                gr_forward_block<DP, HP>(s, GrNoise{nb, noise_step, a.noise_regen, i, N, lane, (unsigned)it, uid, key}, i);
+                if (!REGEN) gr_fill_noise(s, a, nb, i, lane, it, uid, key, noise_step);
+                gr_forward_block<DP, HP, REGEN>(s, GrNoise{nb, noise_step, i, N, lane, (unsigned)it, uid, key}, i);
                 __syncwarp();
             }
             __syncthreads();
@@ -788,8 +794,8 @@ __global__ void __launch_bounds__(GR_NT, 1) graph_kernel(const GraphArgs a) {
                 if (a.dbg_dldp && has && i < N)
                     for (int c = 0; c < s.desc->n_var; ++c) a.dbg_dldp[(size_t(it) * N + i) * s.desc->n_var + c] = gl[c];
                 if (has) {
-                    if (!noise_kept) gr_fill_noise(s, a, nb, i, lane, it, uid, key, noise_step);
-                    gr_backward_block<DP, HP>(s, GrNoise{nb, noise_step, a.noise_regen, i, N, lane, (unsigned)it, uid, key}, i, lane, gl);
+                    if (!REGEN && !noise_kept) gr_fill_noise(s, a, nb, i, lane, it, uid, key, noise_step);
+                    gr_backward_block<DP, HP, REGEN>(s, GrNoise{nb, noise_step, i, N, lane, (unsigned)it, uid, key}, i, lane, gl);
                     __syncwarp();
                 }
             } else {
@@ -839,8 +845,8 @@ __global__ void __launch_bounds__(GR_NT, 1) graph_kernel(const GraphArgs a) {
                     }
                     if (a.dbg_dldp && i < N)
                         for (int c = 0; c < s.desc->n_var; ++c) a.dbg_dldp[(size_t(it) * N + i) * s.desc->n_var + c] = gl[c];
-                    if (!noise_kept) gr_fill_noise(s, a, nb, i, lane, it, uid, key, noise_step);
-                    gr_backward_block<DP, HP>(s, GrNoise{nb, noise_step, a.noise_regen, i, N, lane, (unsigned)it, uid, key}, i, lane, gl);
+                    if (!REGEN && !noise_kept) gr_fill_noise(s, a, nb, i, lane, it, uid, key, noise_step);
+                    gr_backward_block<DP, HP, REGEN>(s, GrNoise{nb, noise_step, i, N, lane, (unsigned)it, uid, key}, i, lane, gl);
                     __syncwarp();
                 }
             }

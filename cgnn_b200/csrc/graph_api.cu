@@ -32,7 +32,9 @@ static __global__ void gather_rows_kernel(const float* __restrict__ data, int n_
 
 #define DECL(DP_)                                                                                  \
     cudaError_t cgnn_launch_graph_dp##DP_##_hp20(int, const GraphArgs&, int, int, size_t, cudaStream_t, int*); \
-    cudaError_t cgnn_launch_graph_dp##DP_##_hp32(int, const GraphArgs&, int, int, size_t, cudaStream_t, int*);
+    cudaError_t cgnn_launch_graph_dp##DP_##_hp32(int, const GraphArgs&, int, int, size_t, cudaStream_t, int*); \
+    cudaError_t cgnn_launch_graph_dp##DP_##_hp20_regen(int, const GraphArgs&, int, int, size_t, cudaStream_t, int*); \
+    cudaError_t cgnn_launch_graph_dp##DP_##_hp32_regen(int, const GraphArgs&, int, int, size_t, cudaStream_t, int*);
 DECL(8) DECL(16) DECL(20) DECL(22) DECL(24) DECL(32)
 #undef DECL
 
@@ -50,6 +52,9 @@ static cudaError_t launch_graph(int dp, int hp, int pol, const GraphArgs& a, int
                                 cudaStream_t st, int* max_clusters) {
 #define CASE(DP_)                                                                                              \
     case DP_:                                                                                                  \
+        if (a.noise_regen)                                                                                     \
+            return hp == 20 ? cgnn_launch_graph_dp##DP_##_hp20_regen(pol, a, n_clusters, csz, smem, st, max_clusters)    \
+                            : cgnn_launch_graph_dp##DP_##_hp32_regen(pol, a, n_clusters, csz, smem, st, max_clusters);   \
         return hp == 20 ? cgnn_launch_graph_dp##DP_##_hp20(pol, a, n_clusters, csz, smem, st, max_clusters)    \
                         : cgnn_launch_graph_dp##DP_##_hp32(pol, a, n_clusters, csz, smem, st, max_clusters);
     switch (dp) { CASE(8) CASE(16) CASE(20) CASE(22) CASE(24) CASE(32) }
