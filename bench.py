@@ -280,7 +280,7 @@ def hill_climbing_leg(world, barrier, max_over_ranks):
                       "few), and the host replays the search between batches" % world}
 
 
-def ragged_leg(world, barrier, max_over_ranks, n_pairs_per_rank=40):
+def ragged_leg(world, barrier, max_over_ranks, n_pairs_per_rank=120):
     """Pairs of different lengths (300 ... 1500 rows, cost ~ rows^2) over the ranks: static equal shards against the
     chunked work-stealing schedule of cgnn_b200/runtime.py (SETTINGS.work_stealing; the reference places run r on
     GPU r % nb_gpu, GNN.py:158-163).  Same pairs, same scores; reports the two wall times and who took which chunks."""
