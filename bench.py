@@ -276,7 +276,7 @@ def hill_climbing_leg(world, barrier, max_over_ranks):
             "edges": len(truth), "edges_correct_after_pairwise": int(pw_hits),
             "edges_correct_after_hill_climbing": int(sum((a, b) in truth for a, b, _ in res.get_list_edges())),
             "limits": "a batch is at most one speculation horizon of candidates (two waves of one GPU per rank); with %d ranks a "
-                      "launch holds the instance counts above against 148 SMs per GPU (instances on clusters of 2-4 CTAs when "
+                      "launch holds the instance counts above against 148 SMs per GPU (instances on clusters of 2-8 CTAs when "
                       "few), and the host replays the search between batches" % world}
 
 

@@ -101,7 +101,7 @@ static inline int check_hp(cgnn_ctx* ctx, const cgnn_hparams* hp) {
         return fail(ctx, CGNN_ERR_LIMIT, "h_layer_dim=%d outside [1,%d]", hp->h_layer_dim, CGNN_MAX_H);
     if (hp->train_epochs < 0 || hp->test_epochs < 0) return fail(ctx, CGNN_ERR_ARG, "negative epoch count");
     if (hp->exp_policy < CGNN_EXP_POLICY_AUTO || hp->exp_policy > 3) return fail(ctx, CGNN_ERR_ARG, "exp_policy=%d unknown", hp->exp_policy);
-    if (hp->graph_cluster < 0 || hp->graph_cluster > 4) return fail(ctx, CGNN_ERR_ARG, "graph_cluster=%d outside [0,4]", hp->graph_cluster);
+    if (hp->graph_cluster < 0 || hp->graph_cluster > 8) return fail(ctx, CGNN_ERR_ARG, "graph_cluster=%d outside [0,8]", hp->graph_cluster);
     if (hp->fast_mmd_vectors < 0 || hp->fast_mmd_vectors > CGNN_MAX_FAST_VECTORS)
         return fail(ctx, CGNN_ERR_LIMIT, "fast_mmd_vectors=%d outside [0,%d]", hp->fast_mmd_vectors, CGNN_MAX_FAST_VECTORS);
     return 0;

@@ -1,5 +1,6 @@
 // C-ABI of the graph path: cgnn_b200_run_graph, cgnn_b200_graph_step_debug.  See include/cgnn_b200.h.
 #include <cmath>
+#include <cstdlib>
 #include <vector>
 
 #include "ctx.h"
@@ -266,11 +267,11 @@ static int run_graph_impl(cgnn_ctx* ctx, const cgnn_hparams* hp, const float* da
     // ---- CTAs per instance: a cluster when the batch cannot fill the GPU with one CTA per instance ----------
     const int NB = NP / 32;
     const int min_csz = a.fast_k > 0 ? (NB + GR_NW - 1) / GR_NW : 1;   // random-feature mode: one row block per warp
-    if (min_csz > 4 || (dbg_host && min_csz > 1))
+    if (min_csz > GR_MAX_CLUSTER || (dbg_host && min_csz > 1))
         return fail(ctx, CGNN_ERR_LIMIT, "random-feature loss on the graph path: n_rows=%d needs a cluster of %d CTAs (limit %d)",
-                    n_rows, min_csz, dbg_host ? 1 : 4);
-    int slots_of[5] = {0, 0, 0, 0, 0};                                  // resident clusters per cluster size
-    for (int csz = min_csz; csz <= 4; ++csz) {
+                    n_rows, min_csz, dbg_host ? 1 : GR_MAX_CLUSTER);
+    int slots_of[GR_MAX_CLUSTER + 1] = {0};                                  // resident clusters per cluster size
+    for (int csz = min_csz; csz <= GR_MAX_CLUSTER; ++csz) {
         if (dbg_host && csz > 1) break;                              // the parity probe runs on one CTA
         if (hp->graph_cluster > 0 && csz != hp->graph_cluster) continue;
         if (hp->graph_cluster == 0 && csz > min_csz && (NB + csz - 1) / csz < 4) continue;   // fixed costs dominate tiny shares
@@ -289,7 +290,7 @@ static int run_graph_impl(cgnn_ctx* ctx, const cgnn_hparams* hp, const float* da
     struct Choice { int csz, slots; double t_inst, cost; };
     auto choose = [&](int n) {
         Choice best{0, 0, 0.0, 1e300};
-        for (int csz = 1; csz <= 4; ++csz) {
+        for (int csz = 1; csz <= GR_MAX_CLUSTER; ++csz) {
             if (slots_of[csz] < 1) continue;
             const int rb_per_cta = (NB + csz - 1) / csz;
             const int tail_w = rb_per_cta % GR_NW;
@@ -311,6 +312,9 @@ static int run_graph_impl(cgnn_ctx* ctx, const cgnn_hparams* hp, const float* da
         if (!(tailc.csz != mainc.csz && tailc.cost < 0.93 * mainc.t_inst)) tailc.csz = 0;
     }
 
+    if (getenv("CGNN_DEBUG"))
+        fprintf(stderr, "[cgnn_b200] graph batch: %d instances, main cluster %d (%d resident), full %d, remainder %d on cluster %d (%d resident)\n",
+                n_inst, mainc.csz, mainc.slots, full, rem, tailc.csz, tailc.slots);
     CU(cudaEventRecord(ctx->ev0, ctx->stream));
     cudaError_t le;
     if (tailc.csz) {

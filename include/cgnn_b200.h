@@ -74,7 +74,7 @@ typedef struct cgnn_hparams {
                                  of Loss.py:35-56 with k = SETTINGS.nb_vectors_approx_MMD vectors per bandwidth
                                  (k <= CGNN_MAX_FAST_VECTORS; on the graph path n_rows <= 2048) */
     unsigned long long seed;  /* engine Philox seed.  The reference is unseeded (no hit for "seed" in its tree). */
-    int   graph_cluster;      /* graph path: CTAs (SMs) per instance, 1..4; 0 = chosen per batch (a thread-block cluster
+    int   graph_cluster;      /* graph path: CTAs (SMs) per instance, 1..8; 0 = chosen per batch (a thread-block cluster
                                  when the batch has too few instances to fill the GPU otherwise) */
     int   graph_noise_regen;  /* graph path: 0 = buffer a row block's noise columns when they fit shared memory (default),
                                  1 = always re-derive them at every use (the plan the engine falls back to when they do

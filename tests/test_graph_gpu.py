@@ -205,7 +205,7 @@ def test_cluster_sizes_agree(engine):
     kw = dict(n_runs=3, h_layer_dim=14, train_epochs=12, test_epochs=4, seed=9, want_params=True, want_trace=True, trace_every=3)
     base = engine.run_graph(data, [plan, plan], graph_cluster=1, **kw)
     assert engine.last_graph_cluster == 1
-    for c in (2, 3, 4):
+    for c in (2, 3, 4, 6, 8):
         r = engine.run_graph(data, [plan, plan], graph_cluster=c, **kw)
         assert engine.last_graph_cluster == c
         assert np.array_equal(r["params"], base["params"]), "cluster size %d changed the trained parameters" % c

@@ -18,7 +18,7 @@ eng = Engine(0)
 
 def run(name, X, plan):
     base = None
-    for c in (0, 1, 2, 3, 4):
+    for c in (0, 1, 2, 3, 4, 5, 6, 8):
         kw = dict(n_runs=n_inst, h_layer_dim=20, train_epochs=train, test_epochs=test, seed=1, graph_cluster=c)
         eng.run_graph(X, [plan], **kw)
         r = eng.run_graph(X, [plan], **kw)
