@@ -92,15 +92,17 @@ class GraphScorer(object):
         return float("nan")
 
     def _horizon(self):
-        """How many unseen candidates one speculative batch may hold: enough instances for two full waves
-        of the graph kernel (one CTA per SM) on every GPU of the job.  A larger batch is no faster per
-        candidate, and everything speculated after an accepted move is wasted."""
+        """How many unseen candidates one speculative batch may hold: enough instances for ONE full wave of the graph
+        kernel (one CTA per SM) on every GPU of the job.  Everything speculated after an accepted move is wasted, and
+        once the GPUs are full a larger batch is no faster per candidate: on the bundled 22-variable example the search
+        needs 33 candidates one by one (6.0 s); one wave per batch scores 38 (3.5 s), two waves 52 (4.1 s), three 64
+        (5.2 s) - tools/bench_horizon.py.  The decisions are the same for every horizon."""
         if self.horizon is None:
             try:
                 slots = sum(e.device_info()["n_sm"] for e in runtime.get_engines()) * runtime.dist_info()[1]
             except Exception:
                 slots = 148
-            self.horizon = max(1, (2 * slots) // max(1, self.nb_runs))
+            self.horizon = max(1, slots // max(1, self.nb_runs))
         return self.horizon
 
     def end_of_sweep(self):
