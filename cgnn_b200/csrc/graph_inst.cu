@@ -40,7 +40,7 @@ cudaError_t CAT(CAT(CAT(cgnn_launch_graph_dp, CGNN_DP), CAT(_hp, CGNN_HP)), CGNN
     switch (pol) {
         case 0: return launch<0>(a, n_clusters, csz, smem, st, max_clusters);
         case 1: return launch<1>(a, n_clusters, csz, smem, st, max_clusters);
-        case 2: return launch<2>(a, n_clusters, csz, smem, st, max_clusters);
+        case 2: return launch<1>(a, n_clusters, csz, smem, st, max_clusters);   // not built for this kernel: 1 is the nearest more accurate policy
         case 3: return launch<3>(a, n_clusters, csz, smem, st, max_clusters);
     }
     return cudaErrorInvalidValue;

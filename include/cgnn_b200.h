@@ -67,7 +67,8 @@ typedef struct cgnn_hparams {
                                  3 = three (+ gamma 5 = 5th power of gamma 1);
                                  CGNN_EXP_POLICY_AUTO (-1) = the fastest measured per path: 3 on the pairwise path
                                  (bound by the MUFU pipe), 1 on the graph path (bound by the FMA pipe, where an
-                                 ex2 is cheaper than the multiplies that replace it) */
+                                 ex2 is cheaper than the multiplies that replace it).  The graph kernel is built for
+                                 0, 1 and 3; it runs a request for 2 as 1 (one ex2 more, smaller error) */
     int   trace_every;        /* >0: also compute the (pre-update) training loss on every trace_every-th
                                  train step into loss_trace (GNN.py:98-102 prints every 100th); 0 = never */
     int   fast_mmd_vectors;   /* 0: Gaussian-kernel MMD (SETTINGS.use_Fast_MMD = False).  k > 0: the random-feature loss
