@@ -8,23 +8,26 @@
 // n_par generated parent columns, then its own noise column, then (confounders only) one shared
 // noise column per skeleton neighbour (CGNN_confounders.py:84-96).
 //
-// Layout: the generated matrix Pm[NP][DP] (row-major, DP = n_var padded to a multiple of 4, pad
+// Layout: the generated matrix Pm[NP][DP] (row-major, DP = n_var padded to 8/16/20/22/24/32, pad
 // columns 0) lives in shared memory for the instance's whole life; the observed matrix T[NP][DP]
 // is the same for every instance of a batch (or one per row subset).  It is copied to shared memory next
 // to Pm when both fit one SM (t_smem); otherwise every warp streams it through a cp.async ring that lives
 // in its (idle) noise buffer, two halves of 16 rows (t_ring); only when neither is possible (random-feature
 // mode, very narrow noise buffers) is it read through the read-only path (L1/L2).  Parameters, Adam moments
-// and the fixed-point gradient accumulators are in shared memory too.
+// and the fixed-point gradient accumulators are in shared memory too.  The host picks the plan from the instance
+// shape (graph_api.cu); models too wide to buffer their noise columns per row block run the REGEN instantiation,
+// which re-derives every noise value from its Philox counter where a node consumes it.
 //
 // Mapping: lane <-> row i.  A warp owns whole 32-row blocks (w, w+NW, ...): the row's generated
 // values, its MMD gradient accumulators and the distance differences stay in REGISTERS across all
 // 2N kernel evaluations of the row, and the row's gradient goes straight into the thread-local
 // MLP backward pass - dLoss/dPred is never written to memory.  Column j (DP floats) arrives as
-// DP/4 128-bit broadcast loads.  Parameter gradients are reduced across the 32 rows of a block with
+// broadcast loads; the gradient pass takes the observed and the generated column j in one iteration, their two
+// kernel-weight chains as one FP32x2 chain (gr_grad_pair).  Parameter gradients are reduced across the 32 rows of a block with
 // the transposing warp reduction and accumulated across warps with fixed-point shared atomics.
 //
 // Thread-block clusters: when a batch has fewer instances than the GPU has SMs (a hill-climbing tail, the
-// 20-variable configuration on 8 GPUs) one instance is given a CLUSTER of 2-4 CTAs.  Every CTA keeps the whole
+// 20-variable configuration on 8 GPUs) one instance is given a CLUSTER of 2-8 CTAs.  Every CTA keeps the whole
 // generated matrix and all parameters (the generator forward is replicated - ~3 % of a step), the row blocks of
 // the MMD / backward pass are split over the CTAs, and once per step the fixed-point gradient accumulators are
 // summed across the cluster through distributed shared memory, so all CTAs apply the same Adam update.
@@ -35,14 +38,6 @@
 namespace cgnn {
 
 namespace cg = cooperative_groups;
-
-#define GR_PRAGMA(x) _Pragma(#x)
-#define GR_UNROLL(n) GR_PRAGMA(unroll n)
-#ifdef CGNN_GRAD_UNROLL
-#define GR_GRAD_UNROLL GR_UNROLL(CGNN_GRAD_UNROLL)
-#else
-#define GR_GRAD_UNROLL
-#endif
 
 #ifndef CGNN_GR_NT
 #define CGNN_GR_NT 512
@@ -330,7 +325,6 @@ __device__ __forceinline__ void gr_mmd_grad_row(const float* __restrict__ Pm, co
         asm volatile("cp.async.wait_group 0;" ::: "memory");
         __syncwarp();
     } else {
-        GR_GRAD_UNROLL
         for (int j = 0; j < N; ++j) gr_grad_pair<DP, POL, TM == GR_T_GMEM>(np, T + size_t(j) * DP, Pm + size_t(j) * DP, acc);
     }
 }
