@@ -106,7 +106,11 @@ class GraphScorer(object):
         return self.horizon
 
     def end_of_sweep(self):
-        if self.pending is not None:
+        # A sweep that ended with unanswered candidates normally ends the speculative run.  If the batch is still
+        # short of a GPU wave it keeps going instead: should the algorithm start another sweep (a move was accepted
+        # earlier in this one), its candidates are speculated on top - assuming, as everywhere, that the pending
+        # ones get rejected - so that a launch is not spent on one or two stragglers.
+        if self.pending is not None and len(self.pending) >= self._horizon():
             raise _Speculating()
 
     def flush(self):
