@@ -56,7 +56,8 @@ def _oracle_steps(data, plan, noise, theta0, h):
 
 @pytest.mark.parametrize("pol", [0, 1, 3])          # 1 is what the graph path runs by default (CGNN_EXP_POLICY_GRAPH)
 @pytest.mark.parametrize("n,n_var,h,conf", [(100, 5, 8, False), (257, 11, 20, False), (64, 22, 20, False),
-                                            (33, 3, 32, False), (96, 8, 12, True), (130, 19, 20, True), (1, 2, 4, False)])
+                                            (33, 3, 32, False), (96, 8, 12, True), (130, 19, 20, True), (1, 2, 4, False),
+                                            (70, 21, 20, False), (45, 23, 24, False), (40, 17, 9, True)])
 def test_graph_step_debug_matches_oracle(engine, n, n_var, h, conf, pol):
     from cgnn_b200.plan import build_plan, n_params
     from oracle import cgnn as oc
