@@ -187,6 +187,11 @@ void cgnn_b200_destroy(cgnn_ctx* ctx) {
         if (b->p) cudaFree(b->p);
     if (ctx->ev0) cudaEventDestroy(ctx->ev0);
     if (ctx->ev1) cudaEventDestroy(ctx->ev1);
+    if (ctx->fork) cudaEventDestroy(ctx->fork);
+    for (int k = 0; k < 2; ++k) {
+        if (ctx->join[k]) cudaEventDestroy(ctx->join[k]);
+        if (ctx->side[k]) cudaStreamDestroy(ctx->side[k]);
+    }
     if (ctx->own_stream && ctx->stream) cudaStreamDestroy(ctx->stream);
     delete ctx;
 }
@@ -335,13 +340,30 @@ static int run_pairwise_impl(cgnn_ctx* ctx, const cgnn_hparams* hp, const float*
         launches.push_back(Launch{b, first, count, std::min(count, per_sm * ctx->prop.multiProcessorCount), smem, np_max});
     }
 
+    // A ragged batch has up to three launches (one per kernel build).  They are independent, so the second and third go
+    // to side streams forked from the caller's stream and joined back into it: the tail of one launch no longer
+    // holds the next one back.
+    if (launches.size() > 1 && !ctx->fork) {
+        CU(cudaEventCreateWithFlags(&ctx->fork, cudaEventDisableTiming));
+        for (int k = 0; k < 2; ++k) {
+            CU(cudaStreamCreateWithFlags(&ctx->side[k], cudaStreamNonBlocking));
+            CU(cudaEventCreateWithFlags(&ctx->join[k], cudaEventDisableTiming));
+        }
+    }
     CU(cudaEventRecord(ctx->ev0, ctx->stream));
+    if (launches.size() > 1) CU(cudaEventRecord(ctx->fork, ctx->stream));
     for (size_t k = 0; k < launches.size(); ++k) {
         const Launch& L = launches[k];
         PairwiseArgs ak = a;
         ak.inst = a.inst + L.first; ak.n_inst = L.count; ak.np_max = L.np_max; ak.counter = a.counter + 16 * int(k);
-        const cudaError_t le = g_pw_builds[L.build].launch(pol, ak, L.grid, L.smem, ctx->stream);
+        cudaStream_t st = k == 0 ? ctx->stream : ctx->side[k - 1];
+        if (k > 0) CU(cudaStreamWaitEvent(st, ctx->fork, 0));
+        const cudaError_t le = g_pw_builds[L.build].launch(pol, ak, L.grid, L.smem, st);
         if (le != cudaSuccess) return fail(ctx, CGNN_ERR_CUDA, "pairwise kernel launch: %s", cudaGetErrorString(le));
+        if (k > 0) {
+            CU(cudaEventRecord(ctx->join[k - 1], st));
+            CU(cudaStreamWaitEvent(ctx->stream, ctx->join[k - 1], 0));
+        }
     }
     CU(cudaEventRecord(ctx->ev1, ctx->stream));
     ctx->last_launches = int(launches.size());

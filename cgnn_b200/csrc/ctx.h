@@ -20,6 +20,8 @@ struct cgnn_ctx {
     cudaStream_t stream = nullptr;
     bool own_stream = true;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    cudaStream_t side[2] = {nullptr, nullptr};       // ragged pairwise batches: the launches of the other kernel builds
+    cudaEvent_t fork = nullptr, join[2] = {nullptr, nullptr};
     cudaDeviceProp prop{};
     std::string err;
     float last_ms = 0.f;
