@@ -26,8 +26,15 @@ _BACKENDS = ("B200", "TensorFlow", "PyTorch")
 
 
 def _say(*a):
+    """The reference's progress prints.  Inside a batched search the algorithm is re-executed once per batch; its lines
+    are held back (search.LOG) and only the final, complete execution is printed - each decision once, as the
+    reference prints it."""
     if SETTINGS.verbose:
-        print(*a)
+        from . import search
+        if search.LOG is not None:
+            search.LOG.append(" ".join(str(x) for x in a))
+        else:
+            print(*a)
 
 
 def run_CGNN_b200(df_data, graph, idx=0, run=0, **kwargs):

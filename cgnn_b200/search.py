@@ -36,6 +36,9 @@ class _Speculating(Exception):
     pass
 
 
+LOG = None      # list of held-back log lines while run_search re-executes an algorithm (see CGNN._say)
+
+
 def structure_key(graph):
     """Order-free identity of a directed graph: the sorted tuple of its edges."""
     return tuple(sorted((str(a), str(b)) for a, b in graph.get_list_edges(order_by_weight=False, return_weights=False)))
@@ -183,13 +186,22 @@ GraphScorer.run_scores_single = _run_scores_single
 
 def run_search(algorithm, graph, scorer, max_rounds=10000):
     """Execute `algorithm(graph_copy, scorer)` by memoised re-execution; returns its final graph."""
-    for _ in range(max_rounds):
-        work = deepcopy(graph)
-        try:
-            result = algorithm(work, scorer)
-            if scorer.pending is None:
-                return result
-        except _Speculating:
-            pass
-        scorer.flush()
+    global LOG
+    try:
+        for _ in range(max_rounds):
+            work = deepcopy(graph)
+            LOG = []
+            try:
+                result = algorithm(work, scorer)
+                if scorer.pending is None:
+                    lines, LOG = LOG, None
+                    for line in lines:                 # the one complete execution: every decision printed once
+                        print(line)
+                    return result
+            except _Speculating:
+                pass
+            LOG = None
+            scorer.flush()
+    finally:
+        LOG = None
     raise RuntimeError("graph search did not converge")

