@@ -300,17 +300,37 @@ static int run_graph_impl(cgnn_ctx* ctx, const cgnn_hparams* hp, const float* da
         }
         return best;
     };
-    const Choice mainc = choose(n_inst);
+    Choice mainc = choose(n_inst);
     if (mainc.csz == 0) return fail(ctx, CGNN_ERR_CUDA, "graph kernel cannot be launched (cluster size %d, %zu B smem)", hp->graph_cluster, smem);
-    ctx->last_cluster = mainc.csz;
-    // A batch just above a multiple of the resident count pays a whole wave for its remainder.  The remainder is
-    // launched on its own, with the cluster size that suits IT (results do not depend on the cluster size).
-    const int full = (n_inst / mainc.slots) * mainc.slots, rem = n_inst - full;
+    // A batch just above a multiple of the resident count pays a whole wave for its remainder.  So the batch may be cut
+    // in two launches: k full waves on clusters of one size, the rest on the cluster size that suits IT (results do not
+    // depend on the cluster size).  Every (size, k) is priced with the model above; the single launch wins ties.
+    int full = n_inst, rem = 0;
     Choice tailc{0, 0, 0.0, 1e300};
-    if (hp->graph_cluster == 0 && !dbg_host && full > 0 && rem > 0) {
-        tailc = choose(rem);
-        if (!(tailc.csz != mainc.csz && tailc.cost < 0.93 * mainc.t_inst)) tailc.csz = 0;
+    if (hp->graph_cluster == 0 && !dbg_host) {
+        double best_cost = mainc.cost;
+        for (int csz = 1; csz <= GR_MAX_CLUSTER; ++csz) {
+            if (slots_of[csz] < 1) continue;
+            const int rb_per_cta = (NB + csz - 1) / csz, tail_w = rb_per_cta % GR_NW;
+            const double t1 = double(rb_per_cta / GR_NW) + (tail_w ? 0.4 + 0.6 * tail_w / GR_NW : 0.0) + (csz > 1 ? 0.06 : 0.0);
+            const int kmax = n_inst / slots_of[csz];
+            for (int k = kmax; k >= 1 && k >= kmax - 2; --k) {
+                const int r = n_inst - k * slots_of[csz];
+                if (r <= 0) continue;
+                const Choice t = choose(r);
+                if (t.csz == 0 || t.csz == csz) continue;
+                const double cost = k * t1 + t.cost + 0.02;           // + a launch boundary
+                if (cost < 0.97 * best_cost) {
+                    best_cost = cost;
+                    mainc = Choice{csz, slots_of[csz], t1, k * t1};
+                    tailc = t;
+                    full = k * slots_of[csz];
+                    rem = r;
+                }
+            }
+        }
     }
+    ctx->last_cluster = mainc.csz;
 
     if (getenv("CGNN_DEBUG"))
         fprintf(stderr, "[cgnn_b200] graph batch: %d instances, main cluster %d (%d resident), full %d, remainder %d on cluster %d (%d resident)\n",
