@@ -393,6 +393,44 @@ __device__ __forceinline__ float warp_reduce_n(const float (&v)[N], int lane, in
     return r;
 }
 
+// Two such reductions at once: lane l ends with the totals of (v[l].x, v[l].y).  The same adds in the same order as
+// two scalar reductions (FADD2 = two IEEE adds), but the two dependent shuffle chains overlap and half the FADD /
+// select instructions disappear.
+template <int N, int OFS>
+struct WarpReduceN2 {
+    static __device__ __forceinline__ float2 run(const float2 (&v)[N], int lane, int& slot, int& n_valid) {
+        constexpr int H = (N + 1) / 2;
+        const bool up = (lane & OFS) != 0;
+        float2 w[H];
+#pragma unroll
+        for (int i = 0; i < H; ++i) {
+            const float2 hi = (H + i < N) ? v[(H + i < N) ? H + i : 0] : make_float2(0.f, 0.f);
+            const float2 send = up ? v[i] : hi;
+            const float2 keep = up ? hi : v[i];
+            w[i] = fadd2(keep, make_float2(__shfl_xor_sync(0xffffffffu, send.x, OFS), __shfl_xor_sync(0xffffffffu, send.y, OFS)));
+        }
+        slot += up ? H : 0;
+        n_valid = up ? max(n_valid - H, 0) : min(n_valid, H);
+        return WarpReduceN2<H, OFS / 2>::run(w, lane, slot, n_valid);
+    }
+};
+template <int N>
+struct WarpReduceN2<N, 0> {
+    static __device__ __forceinline__ float2 run(const float2 (&v)[N], int, int&, int&) {
+        static_assert(N == 1, "32 lanes reduce at most 32 slots");
+        return v[0];
+    }
+};
+template <int N>
+__device__ __forceinline__ float2 warp_reduce_n2(const float2 (&v)[N], int lane, int& slot, bool& valid) {
+    static_assert(N >= 1 && N <= 32, "1..32 slots");
+    slot = 0;
+    int n_valid = N;
+    const float2 r = WarpReduceN2<N, 16>::run(v, lane, slot, n_valid);
+    valid = n_valid >= 1;
+    return r;
+}
+
 // ---------------------------------------------------------------------------------------------
 // TF-1 Adam, fp32, one parameter per call.  lr_t = lr*sqrt(1-b2^t)/(1-b1^t) is computed by the caller.
 // ---------------------------------------------------------------------------------------------

@@ -435,42 +435,50 @@ __device__ __forceinline__ void gr_backward_block(const GrSmem& s, const GrNoise
         // b_out
         const float sb = warp_sum(delta);
         if (lane == 0) fx_add(&s.g64[off + (n_in + 2) * HP], double(sb));
-        // W_out, then dz in place of z.  Sums over the 32 rows: transposing reduction over the HP hidden units;
-        // lane -> (slot, valid) is the same for every reduction of this width
-        float v[HP];
+        // W_out and b_in: sums over the 32 rows by the transposing reduction over the HP hidden units, the two of them
+        // as one packed reduction (lane -> (slot, valid) is the same for every reduction of this width)
+        float2 v[HP];
         int slot;
         bool has_slot;
 #pragma unroll
-        for (int kk = 0; kk < HP; ++kk) v[kk] = fmaxf(gr_zget<HP>(z, kk), 0.f) * delta;
-        float r = warp_reduce_n<HP>(v, lane, slot, has_slot);
-        if (has_slot) fx_add(&s.g64[off + (n_in + 1) * HP + slot], double(r));
-#pragma unroll
         for (int q = 0; q < HP / 2; ++q) {
-            z[q].x = z[q].x > 0.f ? delta * w_out[2 * q] : 0.f;
-            z[q].y = z[q].y > 0.f ? delta * w_out[2 * q + 1] : 0.f;
+            const float2 zq = z[q];
+            z[q].x = zq.x > 0.f ? delta * w_out[2 * q] : 0.f;                 // dz in place of z
+            z[q].y = zq.y > 0.f ? delta * w_out[2 * q + 1] : 0.f;
+            v[2 * q] = make_float2(fmaxf(zq.x, 0.f) * delta, z[q].x);
+            v[2 * q + 1] = make_float2(fmaxf(zq.y, 0.f) * delta, z[q].y);
         }
-        // b_in
+        float2 r = warp_reduce_n2<HP>(v, lane, slot, has_slot);
+        if (has_slot) {
+            fx_add(&s.g64[off + (n_in + 1) * HP + slot], double(r.x));
+            fx_add(&s.g64[off + n_in * HP + slot], double(r.y));
+        }
+        // W_in rows, two inputs per packed reduction, and the input gradients
+        for (int p = 0; p < n_in; p += 2) {
+            const bool two = p + 1 < n_in;
+            const float u0 = (p < n_par) ? s.Pm[i * DP + idx[p]] : gr_noise_get<REGEN>(nz, idx[p]);
+            const float u1 = !two ? 0.f : (p + 1 < n_par) ? s.Pm[i * DP + idx[p + 1]] : gr_noise_get<REGEN>(nz, idx[p + 1]);
 #pragma unroll
-        for (int kk = 0; kk < HP; ++kk) v[kk] = gr_zget<HP>(z, kk);
-        r = warp_reduce_n<HP>(v, lane, slot, has_slot);
-        if (has_slot) fx_add(&s.g64[off + n_in * HP + slot], double(r));
-        // W_in rows and input gradients
-        for (int p = 0; p < n_in; ++p) {
-            const float u = (p < n_par) ? s.Pm[i * DP + idx[p]] : gr_noise_get<REGEN>(nz, idx[p]);
+            for (int kk = 0; kk < HP; ++kk) { const float dz = gr_zget<HP>(z, kk); v[kk] = make_float2(u0 * dz, u1 * dz); }
+            r = warp_reduce_n2<HP>(v, lane, slot, has_slot);
+            if (has_slot) {
+                fx_add(&s.g64[off + p * HP + slot], double(r.x));
+                if (two) fx_add(&s.g64[off + (p + 1) * HP + slot], double(r.y));
+            }
 #pragma unroll
-            for (int kk = 0; kk < HP; ++kk) v[kk] = u * gr_zget<HP>(z, kk);
-            r = warp_reduce_n<HP>(v, lane, slot, has_slot);
-            if (has_slot) fx_add(&s.g64[off + p * HP + slot], double(r));
-            if (p < n_par) {
-                const float4* w4 = reinterpret_cast<const float4*>(s.theta + off + p * HP);
-                float2 du = make_float2(0.f, 0.f);
+            for (int e = 0; e < 2; ++e) {
+                const int pe = p + e;
+                if (pe < n_par) {
+                    const float4* w4 = reinterpret_cast<const float4*>(s.theta + off + pe * HP);
+                    float2 du = make_float2(0.f, 0.f);
 #pragma unroll
-                for (int q = 0; q < HP / 4; ++q) {
-                    const float4 w = w4[q];
-                    du = ffma2(z[2 * q], make_float2(w.x, w.y), du);
-                    du = ffma2(z[2 * q + 1], make_float2(w.z, w.w), du);
+                    for (int q = 0; q < HP / 4; ++q) {
+                        const float4 w = w4[q];
+                        du = ffma2(z[2 * q], make_float2(w.x, w.y), du);
+                        du = ffma2(z[2 * q + 1], make_float2(w.z, w.w), du);
+                    }
+                    gl[idx[pe]] += du.x + du.y;
                 }
-                gl[idx[p]] += du.x + du.y;
             }
         }
     }
