@@ -37,3 +37,25 @@ def test_algorithmic_work_matches_survey():
     assert abs(flops - 132.7e6) < 0.1e6                               # 132.7 MFLOP per train step
     _, f_eval = bench.algorithmic_work(1, 1500, 0, 1)
     assert abs(f_eval - 67.5e6) < 0.1e6
+
+
+def test_executed_roofline_is_recomputable_from_the_tracked_profile():
+    """roofline.frac = max(executed ex2/s / MUFU peak, FMA-pipe lane-slots/s / (FP32 peak / 2)) with the per-evaluation counts
+    of profiles/r2_roofline_*.json; the profile carries the hash of the kernel sources and a mismatch is flagged."""
+    sys.path.insert(0, ROOT)
+    import bench
+    from cgnn_b200.build import source_hash
+    prof = bench.load_profile("pairwise")
+    assert prof is not None and prof["per_eval"]["mufu_lane_ops"] > 0
+    assert prof["stale"] == (prof["source_hash"] != source_hash("pairwise"))
+    evals_per_s, mufu_peak, fp32_peak = 1.4e12, 4.63e12, 73.5e12
+    ex = bench.executed_roofline(prof, evals_per_s, mufu_peak, fp32_peak)
+    assert abs(ex["mufu_frac"] - prof["per_eval"]["mufu_lane_ops"] * evals_per_s / mufu_peak) < 1e-12
+    assert abs(ex["fma_pipe_frac"] - prof["per_eval"]["fma_pipe_lane_slots"] * evals_per_s / (fp32_peak / 2)) < 1e-12
+    assert 0 < ex["mufu_frac"] < 1 and 0 < ex["fma_pipe_frac"] < 1
+    w = prof["warp_inst"]                      # slots = (scalar + 2 x packed) x 32 / evaluations, as the note in the file says
+    evals = prof["workload"]["evals_per_launch"]
+    assert abs(prof["per_eval"]["fma_pipe_lane_slots"] - (w["fma_pipe_scalar"] + 2 * w["fma_pipe_packed_f32x2"]) * 32.0 / evals) < 1e-9
+    for which in ("graph_c2", "graph_c5"):
+        g = bench.load_profile(which)
+        assert g is not None and g["stale"] == (g["source_hash"] != source_hash("graph"))
