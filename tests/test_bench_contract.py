@@ -48,6 +48,8 @@ def test_executed_roofline_is_recomputable_from_the_tracked_profile():
     prof = bench.load_profile("pairwise")
     assert prof is not None and prof["per_eval"]["mufu_lane_ops"] > 0
     assert prof["stale"] == (prof["source_hash"] != source_hash("pairwise"))
+    assert not prof["stale"], "cgnn_b200/csrc changed after profiles/r2_roofline_pairwise.json was captured: re-run the ncu capture " \
+                              "(tools/profile_target.py under ncu --set full, then tools/ncu_summary.py --json)"
     evals_per_s, mufu_peak, fp32_peak = 1.4e12, 4.63e12, 73.5e12
     ex = bench.executed_roofline(prof, evals_per_s, mufu_peak, fp32_peak)
     assert abs(ex["mufu_frac"] - prof["per_eval"]["mufu_lane_ops"] * evals_per_s / mufu_peak) < 1e-12
@@ -59,3 +61,4 @@ def test_executed_roofline_is_recomputable_from_the_tracked_profile():
     for which in ("graph_c2", "graph_c5"):
         g = bench.load_profile(which)
         assert g is not None and g["stale"] == (g["source_hash"] != source_hash("graph"))
+        assert not g["stale"], "graph kernel sources changed after profiles/%s was captured" % bench.PROFILE_FILES[which]
