@@ -12,7 +12,7 @@ import cgnn_b200 as cgnn
 from cgnn_b200 import synth
 
 n_pairs = int(sys.argv[1]) if len(sys.argv) > 1 else 1000
-out = sys.argv[2] if len(sys.argv) > 2 else "gpurun_out/r1_config4.json"
+out = sys.argv[2] if len(sys.argv) > 2 else "gpurun_out/r2_config4.json"
 rank, world, local = int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_SIZE", 1)), int(os.environ.get("LOCAL_RANK", 0))
 torch.cuda.set_device(local)
 if world > 1:

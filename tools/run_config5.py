@@ -11,7 +11,7 @@ import cgnn_b200 as cgnn
 from cgnn_b200 import synth
 from cgnn_b200.CGNN import hill_climbing
 
-out = sys.argv[1] if len(sys.argv) > 1 else "gpurun_out/r1_config5.json"
+out = sys.argv[1] if len(sys.argv) > 1 else "gpurun_out/r2_config5.json"
 rank, world, local = int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_SIZE", 1)), int(os.environ.get("LOCAL_RANK", 0))
 torch.cuda.set_device(local)
 if world > 1:
